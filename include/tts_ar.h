@@ -1,0 +1,176 @@
+/* tts_ar.h -- C ABI of the B200-native UnifiedVoice autoregressive (AR) mel-code sampler.
+ *
+ * Drop-in boundary for ONE path of e-c-k-e-r/tortoise-tts: everything below
+ * `UnifiedVoice.inference_speech / compute_embeddings+get_generator / forward(return_latent=True)`
+ * (reference tortoise_tts/models/unified_voice.py:614-679, 544-600), i.e. the GPT-2 prefill, the
+ * KV-cached per-step decode, the mel head and the HF logits processors + sample loop
+ * (reference tortoise_tts/models/stream_generator.py:56-101, 1106-1190).  The reference has no FFI of
+ * its own (it is 100% Python over torch/HF); the Python adapter `tortoise_tts_b200.UnifiedVoiceB200`
+ * keeps the reference's method signatures and binds these entry points with ctypes
+ * (see INTEGRATION.md).  Plain C: opaque handle, raw pointers and sizes, no torch / C++ types.
+ *
+ * Conventions
+ *  - every call returns 0 on success or a negative TtsArStatus; nothing aborts or throws.
+ *  - `stream` is a cudaStream_t passed as void*; all device work is enqueued on it; calls do not
+ *    synchronise unless documented ("SYNC").  One handle == one device; calls on a handle must be
+ *    serialised by the caller (the reference model object is not re-entrant either:
+ *    GPT2InferenceModel.cached_mel_emb, unified_voice.py:109,143-144).
+ *  - "dev" pointers are device memory owned by the caller (e.g. torch tensors); "host" pointers are
+ *    ordinary host memory.
+ */
+#ifndef TTS_AR_H_
+#define TTS_AR_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TTS_AR_ABI_VERSION 1
+#define TTS_AR_MODEL_DIM 1024   /* compiled-in: d_model, 16 heads x 64 (unified_voice.py:336-338) */
+#define TTS_AR_HEADS 16
+#define TTS_AR_HEAD_DIM 64
+
+typedef enum {
+  TTS_AR_OK = 0,
+  TTS_AR_ERR_BAD_ARG = -1,      /* reference raises AssertionError / ValueError here */
+  TTS_AR_ERR_CAPACITY = -2,     /* batch / length exceeds what tts_ar_create was sized for */
+  TTS_AR_ERR_CUDA = -3,         /* a CUDA call failed; tts_ar_last_error() has the text */
+  TTS_AR_ERR_STATE = -4,        /* call order: weights not loaded / prefill not done */
+  TTS_AR_ERR_DEVICE = -5,       /* not an sm_100 device, or cooperative launch unsupported */
+  TTS_AR_ERR_WATCHDOG = -6      /* a device-side wait timed out (reported by tts_ar_sync_result) */
+} TtsArStatus;
+
+typedef struct TtsArHandle TtsArHandle;
+
+/* Model geometry (defaults = UnifiedVoice.__init__, unified_voice.py:335-354) + capacity. */
+typedef struct {
+  int32_t struct_size;          /* sizeof(TtsArConfig), for ABI checks */
+  int32_t device;               /* CUDA device ordinal */
+  int32_t n_layers;             /* 30 */
+  int32_t model_dim;            /* must equal TTS_AR_MODEL_DIM */
+  int32_t n_heads;              /* must equal TTS_AR_HEADS */
+  int32_t n_mel_codes;          /* 8194 (rows of mel_embedding / mel_head) */
+  int32_t n_text_rows;          /* 256 (rows of text_embedding) */
+  int32_t n_mel_pos;            /* 608 rows of mel_pos_embedding */
+  int32_t n_text_pos;           /* 404 rows of text_pos_embedding */
+  int32_t start_text_token;     /* 255 */
+  int32_t stop_text_token;      /* 0 */
+  int32_t start_mel_token;      /* 8192 */
+  int32_t stop_mel_token;       /* 8193 (eos == pad, unified_voice.py:664) */
+  int32_t max_utts;             /* capacity: utterances per prefill */
+  int32_t max_seqs;             /* capacity: sequences (utterances x candidates) */
+  int32_t max_text_len;         /* capacity: text tokens per utterance (<= n_text_pos - 2) */
+  int32_t max_new_tokens;       /* capacity: generated tokens per sequence (<= n_mel_pos - 2) */
+} TtsArConfig;
+
+/* One GPT-2 block; names are the reference state_dict keys under gpt.h.{i}..
+ * Conv1D weights are [in, out] row-major exactly as stored by HF. */
+typedef struct {
+  const void *ln_1_w, *ln_1_b;          /* [1024] */
+  const void *c_attn_w, *c_attn_b;      /* [1024,3072], [3072] */
+  const void *attn_proj_w, *attn_proj_b;/* [1024,1024], [1024] */
+  const void *ln_2_w, *ln_2_b;          /* [1024] */
+  const void *c_fc_w, *c_fc_b;          /* [1024,4096], [4096] */
+  const void *mlp_proj_w, *mlp_proj_b;  /* [4096,1024], [1024] */
+} TtsArLayerWeights;
+
+typedef struct {
+  int32_t struct_size;
+  int32_t dtype;                        /* 0 = float32, 1 = bfloat16 (all tensors, dev pointers) */
+  int32_t n_layers;
+  const TtsArLayerWeights* layers;      /* host array of n_layers entries (dev pointers inside) */
+  const void *ln_f_w, *ln_f_b;          /* gpt.ln_f */
+  const void *final_norm_w, *final_norm_b;
+  const void *mel_head_w, *mel_head_b;  /* [n_mel_codes,1024] (nn.Linear [out,in]), [n_mel_codes] */
+  const void *mel_embedding;            /* [n_mel_codes,1024] */
+  const void *mel_pos_embedding;        /* [n_mel_pos,1024] */
+  const void *text_embedding;           /* [n_text_rows,1024] */
+  const void *text_pos_embedding;       /* [n_text_pos,1024] */
+} TtsArWeights;
+
+/* hf_generate_kwargs the reference's callers pass (inference.py:334-346, train.py:119-129). */
+typedef struct {
+  int32_t struct_size;
+  int32_t do_sample;            /* 0: argmax of processed scores (HF greedy) */
+  float temperature;            /* TemperatureLogitsWarper, skipped when == 1 */
+  int32_t top_k;                /* TopKLogitsWarper, 0 = off */
+  float top_p;                  /* TopPLogitsWarper, >= 1 = off */
+  float repetition_penalty;     /* RepetitionPenaltyLogitsProcessor over ALL ids incl. dummy prompt */
+  uint64_t seed;                /* Philox key */
+  int64_t seq_index_base;       /* global index of local sequence 0 (multi-GPU invariance) */
+  int32_t ignore_eos;           /* benchmarking: never finish, run exactly max_new steps */
+  int32_t reserved;
+} TtsArSampling;
+
+typedef struct {
+  int32_t struct_size;
+  int32_t steps_run;            /* columns of out_codes that are valid */
+  int32_t all_finished;
+  int32_t watchdog;             /* != 0: a device-side wait timed out, results invalid */
+  int64_t kernel_launches;      /* launches of this library's kernels since create */
+  double last_algorithmic_bytes;/* SURVEY.md 8(d) bytes of the last generate/step call */
+  float last_device_ms;         /* CUDA-event time of the last prefill+generate on its stream */
+  float last_prefill_ms;
+} TtsArStats;
+
+int tts_ar_abi_version(void);
+
+/* Allocates device state (KV page pool, activations, packed-weight arena). SYNC. */
+int tts_ar_create(const TtsArConfig* cfg, TtsArHandle** out);
+void tts_ar_destroy(TtsArHandle* h);
+const char* tts_ar_last_error(TtsArHandle* h);   /* h may be NULL: error of the last failed create */
+
+/* Snapshot + repack the module's weights (replaces the state_dict the reference model owns;
+ * call again after load_state_dict / LoRA merge, reference lora.py:197-205). */
+int tts_ar_load_weights(TtsArHandle* h, const TtsArWeights* w, void* stream);
+
+/* Prefix build + prompt pass.  Replaces inference_speech lines unified_voice.py:639-650 and the
+ * prefill branch of GPT2InferenceModel.forward (:203-211) for `n_utt` utterances, each expanded to
+ * `n_cand` candidates (num_return_sequences; stream_generator.py:618-623).
+ *   latent   dev float32 [n_utt, 1024]
+ *   text     dev int32   [n_utt, text_stride]  (un-padded ids; start/stop are added here)
+ *   text_len host int32  [n_utt]               (each utterance runs at its true length) */
+int tts_ar_prefill(TtsArHandle* h, const float* latent, const int32_t* text, int32_t text_stride,
+                   const int32_t* text_len, int32_t n_utt, int32_t n_cand, void* stream);
+
+/* The sample loop (stream_generator.py:1106-1190 / HF _sample): up to `max_new` tokens per sequence.
+ *   out_codes   dev int64 [n_seq, max_new]   finished rows are padded with stop_mel_token (Q7)
+ *   out_latents dev float32 [n_seq, max_new, 1024] or NULL: final_norm(hidden) per step (:1172)
+ *   forced      dev int32 [n_seq, max_new] or NULL: teacher forcing (parity hook)
+ *   out_choice  dev int32 [n_seq, max_new] or NULL: the sampler's own pick per step */
+int tts_ar_generate(TtsArHandle* h, const TtsArSampling* s, int32_t max_new, int64_t* out_codes,
+                    float* out_latents, const int32_t* forced, int32_t* out_choice, void* stream);
+
+/* Streaming variant for get_generator (unified_voice.py:670-679): `n_steps` more tokens, state kept.
+ * Same buffers as above with max_new := n_steps. */
+int tts_ar_step(TtsArHandle* h, const TtsArSampling* s, int32_t n_steps, int64_t* out_codes,
+                float* out_latents, const int32_t* forced, int32_t* out_choice, void* stream);
+
+/* Parity hook: the logits the NEXT sample would use.  out dev float32 [rows, n_mel_codes];
+ * rows = n_utt right after prefill, n_seq after any step.  *rows_out is written on return. */
+int tts_ar_logits_debug(TtsArHandle* h, float* out, int32_t* rows_out, void* stream);
+
+/* UnifiedVoice.forward(..., return_latent=True, clip_inputs=False) (unified_voice.py:544-600).
+ *   latent dev float32 [n, 1024]; text dev int32 [n, text_stride] + host text_len[n];
+ *   codes dev int32 [n, codes_stride] + host codes_len[n];
+ *   out dev float32 [n, codes_stride, 1024] (rows >= codes_len[i] are left untouched) */
+int tts_ar_forward_latents(TtsArHandle* h, const float* latent, const int32_t* text, int32_t text_stride,
+                           const int32_t* text_len, const int32_t* codes, int32_t codes_stride,
+                           const int32_t* codes_len, int32_t n, float* out, void* stream);
+
+/* Whole inference_speech call on HOST buffers: H2D of latent/text, prefill, generate, D2H of the
+ * codes, all on `stream`, then waits for it.  SYNC.  This is the end-to-end entry bench.py times. */
+int tts_ar_inference_speech_host(TtsArHandle* h, const float* latent_host, const int32_t* text_host,
+                                 int32_t text_stride, const int32_t* text_len, int32_t n_utt,
+                                 int32_t n_cand, const TtsArSampling* s, int32_t max_new,
+                                 int64_t* out_codes_host, int32_t* steps_run);
+
+/* Waits for `stream`, then reports the last call's outcome. SYNC. */
+int tts_ar_sync_result(TtsArHandle* h, TtsArStats* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TTS_AR_H_ */

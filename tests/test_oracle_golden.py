@@ -1,0 +1,110 @@
+"""CPU: the oracle restatement (oracle/uv_oracle.py) against golden vectors produced by the
+reference's own classes (oracle/make_golden.py).  fp32 tolerance 1e-4 relative (BASELINE.json)."""
+import ast
+import os
+
+import numpy as np
+import torch
+
+from oracle import philox
+from oracle.uv_oracle import (OracleAR, apply_repetition_penalty, apply_temperature, apply_top_k,
+                              apply_top_p)
+from oracle.weights import ARConfig, make_inputs, make_state_dict
+
+FP32_REL = 1e-4
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-30)
+
+
+def test_philox_known_answers():
+    # Random123 kat_vectors, philox4x32-10
+    assert philox.philox4x32_10((0, 0, 0, 0), (0, 0)) == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+    assert philox.philox4x32_10((0xffffffff,) * 4, (0xffffffff,) * 2) == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
+    assert philox.philox4x32_10((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0)) == \
+        [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
+    u = philox.uniform(1234, 5, 7)
+    assert 0.0 <= float(u) < 1.0
+
+
+def test_oracle_matches_reference_l2(golden_dir):
+    g = np.load(os.path.join(golden_dir, "ref_l2.npz"))
+    spec = ast.literal_eval(str(g["spec"]))
+    cfg = ARConfig(layers=spec["layers"])
+    sd = make_state_dict(cfg, seed=spec["w_seed"], attn_std=spec["attn_std"])
+    lat, texts = make_inputs(cfg, spec["n_utt"], [spec["text_len"]] * spec["n_utt"], seed=spec["in_seed"])
+    text = torch.stack(texts)
+    o = OracleAR(sd, cfg)
+    r = o.generate(lat, text, n_cand=spec["n_cand"], max_new=spec["max_new"], want_logits=3,
+                   repetition_penalty=spec["repetition_penalty"])
+    assert np.array_equal(r["codes"].numpy(), g["codes"])                  # greedy ids, bit-exact
+    assert r["pos_trace"] == g["pos_trace"].tolist() == [0] + list(range(2, spec["max_new"] + 1))  # Q2
+    assert r["prefix_len"] == int(g["prefix_len"]) == spec["text_len"] + 3                     # Q3/Q9
+    assert rel(r["logits"].numpy(), g["logits"]) < FP32_REL
+    assert rel(r["latents"].numpy(), g["latents"]) < FP32_REL
+    codes = torch.from_numpy(g["reforward_codes"])
+    lat2, text2 = lat.repeat_interleave(2, 0), text.repeat_interleave(2, 0)
+    assert rel(o.forward_latents(lat2, text2, codes).numpy(), g["reforward_latents"]) < FP32_REL
+
+
+def test_oracle_matches_reference_full_c1_prefix(golden_dir):
+    """Config C1 at full depth: the first 12 greedy steps (the whole 200 run in the GPU tests and bench)."""
+    g = np.load(os.path.join(golden_dir, "ref_full_c1.npz"))
+    cfg = ARConfig()
+    sd = make_state_dict(cfg, seed=0)
+    lat, texts = make_inputs(cfg, 1, [64], seed=1)
+    torch.set_num_threads(os.cpu_count() or 1)
+    r = OracleAR(sd, cfg).generate(lat, torch.stack(texts), max_new=12, ignore_eos=True, want_logits=2)
+    assert np.array_equal(r["codes"].numpy(), g["codes"][:, :12])
+    assert rel(r["logits"].numpy(), g["logits_first"]) < FP32_REL
+    assert rel(r["latents"][:, :2].numpy(), g["latents_sel"][:, :2]) < FP32_REL
+    assert int(g["prefix_len"]) == 67
+
+
+def test_warpers_match_hf(golden_dir):
+    g = np.load(os.path.join(golden_dir, "hf_warpers.npz"))
+    logits, ids = torch.from_numpy(g["logits"]), torch.from_numpy(g["ids"])
+    assert torch.equal(apply_repetition_penalty(logits, ids, 2.0), torch.from_numpy(g["rep2"]))
+    assert torch.allclose(apply_temperature(logits, 0.8), torch.from_numpy(g["temp08"]), rtol=0, atol=0)
+    assert np.array_equal(torch.isfinite(apply_top_k(logits, 16)).numpy(), g["topk16"])
+    for p in (0.8, 0.5, 0.95):
+        assert np.array_equal(torch.isfinite(apply_top_p(logits, p)).numpy(), g[f"topp{int(p * 100)}"])
+    chain = apply_top_p(apply_top_k(apply_temperature(apply_repetition_penalty(logits, ids, 2.0), 0.8), 50), 0.8)
+    assert np.array_equal(torch.isfinite(chain).numpy(), np.isfinite(g["chain"]))
+    fin = np.isfinite(g["chain"])
+    assert np.allclose(chain.numpy()[fin], g["chain"][fin], rtol=1e-6)
+
+
+def test_top_p_mass_rule_equals_hf_support(golden_dir):
+    """The device sampler keeps token i iff (probability mass of strictly larger scores) < top_p.
+    That is HF's `cumsum(ascending) <= 1-p -> remove` rule without the sort; check the two support
+    sets are identical on the HF golden rows."""
+    g = np.load(os.path.join(golden_dir, "hf_warpers.npz"))
+    logits = g["logits"].astype(np.float64)
+    for p in (0.8, 0.5, 0.95):
+        want = g[f"topp{int(p * 100)}"]
+        for r in range(logits.shape[0]):
+            e = np.exp(logits[r] - logits[r].max())
+            pr = e / e.sum()
+            order = np.argsort(-logits[r], kind="stable")
+            above = np.zeros_like(pr)
+            above[order] = np.concatenate([[0.0], np.cumsum(pr[order])[:-1]])
+            assert np.array_equal(above < p, want[r])
+
+
+def test_multinomial_row_is_inverse_cdf():
+    rng = np.random.default_rng(0)
+    s = rng.standard_normal(50).astype(np.float32)
+    s[rng.random(50) < 0.5] = -np.inf
+    s[7] = 3.0
+    counts = np.zeros(50)
+    for i in range(4000):
+        tok, _ = philox.multinomial_row(s, philox.uniform(99, i, 0))
+        counts[tok] += 1
+    assert counts[~np.isfinite(s)].sum() == 0
+    e = np.where(np.isfinite(s), np.exp(s - s.max()), 0)
+    pr = e / e.sum()
+    chi2 = (((counts - 4000 * pr) ** 2) / np.maximum(4000 * pr, 1e-9))[pr > 0].sum()
+    assert chi2 < 2.0 * (pr > 0).sum() + 30
