@@ -1,0 +1,226 @@
+// ar_core.cuh -- control block, weight-stream pipeline, grid barrier and LayerNorm staging of the
+// persistent interpreter kernel.
+#pragma once
+#include "ar_params.h"
+#include "dev_utils.cuh"
+
+namespace tts {
+
+constexpr int kMaxSlots = 12;
+
+struct Ctrl {
+  uint64_t full[kMaxSlots];    // producer -> consumers: chunk landed (tx-count barrier)
+  uint64_t empty[kMaxSlots];   // consumers -> producer: slot free again (16 warp arrivals)
+  float scratch[32];
+  volatile int abort_flag;     // a wait timed out somewhere: fall through everything
+  volatile int stop_flag;      // consumers are done (normal end or early exit)
+  volatile uint32_t stop_ci;   // chunks the consumers actually consumed
+  int ibuf[8];
+};
+
+struct Smem {
+  Ctrl* ctrl;
+  uint8_t* a_rm;     // LN'd A operand, bf16 row-major, rows padded to kARowBytes (ldmatrix source)
+  float* red;        // cross-warp reduction buffer / sampler scratch / attention plan copy
+  uint8_t* ring;     // n_slots * kChunkBytes of streamed weights
+};
+
+__device__ __forceinline__ Smem carve_smem(uint8_t* base, int mt_max) {
+  Smem s;
+  s.ctrl = reinterpret_cast<Ctrl*>(base);
+  s.a_rm = base + kSmemCtrlBytes;
+  s.red = reinterpret_cast<float*>(s.a_rm + smem_a_bytes(mt_max));
+  s.ring = reinterpret_cast<uint8_t*>(s.red) + kSmemRedBytes;
+  return s;
+}
+
+// Consumer-side view of the weight stream: every consumer warp consumes every chunk, in order.
+struct Pipe {
+  uint32_t ci;      // chunks consumed so far
+  uint32_t slot;    // ci % n_slots
+  uint32_t phase;   // (ci / n_slots) & 1
+  int n_slots;
+  __device__ __forceinline__ void advance() {
+    ++ci;
+    if (++slot == (uint32_t)n_slots) { slot = 0; phase ^= 1; }
+  }
+};
+
+// What a GEMM-type instruction streams.
+struct GemmDesc {
+  const uint4* w;     // packed chunks
+  int K;              // 1024 or 4096
+  int n_tiles;        // N / 8 (head: ceil(V/8))
+};
+
+__device__ __forceinline__ bool gemm_desc(const Params& P, const Instr& ins, GemmDesc& d) {
+  switch (ins.op) {
+    case OP_LN_QKV: d.w = P.layers[ins.layer].w_qkv; d.K = kD; d.n_tiles = kD3 / 8; return true;
+    case OP_PROJ:   d.w = P.layers[ins.layer].w_proj; d.K = kD; d.n_tiles = kD / 8; return true;
+    case OP_LN_FC:  d.w = P.layers[ins.layer].w_fc; d.K = kD; d.n_tiles = kD4 / 8; return true;
+    case OP_PROJ2:  d.w = P.layers[ins.layer].w_proj2; d.K = kD4; d.n_tiles = kD / 8; return true;
+    case OP_HEAD:   d.w = P.w_head; d.K = kD; d.n_tiles = P.v_tiles; return true;
+    default: return false;
+  }
+}
+
+// Is instruction `pc` of step `step` executed?  (generate() does not run the model after the last token.)
+__device__ __forceinline__ bool instr_live(const Params& P, int step, const Instr& ins) {
+  return !(P.skip_last_model && step == P.n_steps - 1 && ins.op != OP_SAMPLE);
+}
+
+// ---- producer warp: streams this CTA's weight chunks for the whole launch, ahead of the barriers --------
+__device__ void producer_loop(const Params& P, Ctrl* c, uint8_t* ring) {
+  if ((threadIdx.x & 31) != 0) return;
+  const uint64_t pol = make_evict_first_policy();
+  const int cta = blockIdx.x;
+  uint32_t pi = 0, slot = 0, round = 0;
+  bool stopped = false;
+  for (int step = 0; step < P.n_steps && !stopped; ++step) {
+    for (int pc = 0; pc < P.n_instr && !stopped; ++pc) {
+      const Instr ins = P.prog[pc];
+      GemmDesc gd;
+      if (!instr_live(P, step, ins) || !gemm_desc(P, ins, gd)) continue;
+      int t0, cnt;
+      tile_range(gd.n_tiles, P.G, ins.rot, cta, &t0, &cnt);
+      const int kq = gd.K / kChunkK;
+      const uint4* src = gd.w + (size_t)t0 * kq * (kChunkBytes / 16);
+      for (int j = 0; j < cnt * kq; ++j) {
+        if (round > 0) {
+          const uint32_t par = (round - 1) & 1;
+          long long t_start = clock64();
+          while (!mbar_try_wait(&c->empty[slot], par)) {
+            if (c->stop_flag || c->abort_flag) { stopped = true; break; }
+            if (clock64() - t_start > kWatchdogCycles) { c->abort_flag = 1; stopped = true; break; }
+          }
+          if (stopped) break;
+        }
+        mbar_arrive_expect_tx(&c->full[slot], kChunkBytes);
+        bulk_g2s(ring + (size_t)slot * kChunkBytes, src + (size_t)j * (kChunkBytes / 16), kChunkBytes, &c->full[slot], pol);
+        ++pi;
+        if (++slot == (uint32_t)P.n_slots) { slot = 0; ++round; }
+      }
+    }
+  }
+  // Drain: never leave the kernel with bulk copies still landing in this CTA's shared memory.
+  long long t_start = clock64();
+  while (!c->stop_flag) {
+    if (c->abort_flag || clock64() - t_start > kWatchdogCycles) return;
+  }
+  for (uint32_t k = c->stop_ci; k < pi; ++k) {
+    if (!mbar_wait(&c->full[k % P.n_slots], (k / P.n_slots) & 1, &c->abort_flag)) return;
+  }
+}
+
+// ---- grid-wide barrier over the consumer threads of all CTAs --------------------------------------------
+__device__ __forceinline__ bool grid_barrier(const Params& P, Ctrl* c, uint32_t& epoch) {
+  consumer_sync();
+  ++epoch;
+  if (threadIdx.x == 0) {
+    __threadfence();
+    red_release_add_u32(P.bar_counter, 1u);
+    const uint32_t target = epoch * (uint32_t)P.G;
+    long long t0 = clock64();
+    uint32_t spins = 0;
+    while (ld_acquire_u32(P.bar_counter) < target) {
+      if ((++spins & 255u) == 0) {
+        if (c->abort_flag || __ldcg(P.watchdog) || clock64() - t0 > kWatchdogCycles) {
+          c->abort_flag = 1;
+          *reinterpret_cast<volatile int*>(P.watchdog) = 1;
+          break;
+        }
+      }
+    }
+    __threadfence();
+  }
+  consumer_sync();
+  return c->abort_flag == 0;
+}
+
+// ---- LayerNorm of up to 64 rows into the shared bf16 A operand ------------------------------------------------
+// Warp w normalises rows w, w+16, ... (fp32 statistics, two-pass, eps 1e-5 = nn.LayerNorm default used by
+// HF GPT2Block and by final_norm).  kDouble: ln_f then final_norm (reference quirk Q1,
+// unified_voice.py:106,239); CTA 0 also publishes the fp32 result as the step latent
+// (stream_generator.py:1172).  Rows >= nrows of the last M-tile are zero-filled.
+template <bool kDouble>
+__device__ void ln_rows_to_smem(const Params& P, const Instr& ins, uint8_t* a_rm, const float* g1, const float* b1,
+                                const float* g2, const float* b2, int mt_count) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int r = w; r < mt_count * 16; r += kNW) {
+    uint8_t* dst = a_rm + (size_t)r * kARowBytes;
+    if (r >= ins.nrows) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) *reinterpret_cast<uint2*>(dst + (128 * j + 4 * lane) * 2) = make_uint2(0u, 0u);
+      continue;
+    }
+    const int lrow = ins.row0 + r;                                    // logical row (logits / latent row)
+    const int xrow = (ins.flags & F_ROW_MAP) ? P.head_rows[lrow] : lrow;
+    const float* xp = P.x + (size_t)xrow * kD;
+    float4 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = ld_cg_f4(xp + 128 * j + 4 * lane);
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
+    const float mean = warp_sum(s) * (1.0f / kD);
+    float ss = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float a = v[j].x - mean, b = v[j].y - mean, c2 = v[j].z - mean, d = v[j].w - mean;
+      ss += (a * a + b * b) + (c2 * c2 + d * d);
+    }
+    const float rstd = rsqrtf(warp_sum(ss) * (1.0f / kD) + 1e-5f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float4 g = *reinterpret_cast<const float4*>(g1 + 128 * j + 4 * lane);
+      const float4 b = *reinterpret_cast<const float4*>(b1 + 128 * j + 4 * lane);
+      v[j].x = (v[j].x - mean) * rstd * g.x + b.x;
+      v[j].y = (v[j].y - mean) * rstd * g.y + b.y;
+      v[j].z = (v[j].z - mean) * rstd * g.z + b.z;
+      v[j].w = (v[j].w - mean) * rstd * g.w + b.w;
+    }
+    if (kDouble) {
+      float s2 = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s2 += (v[j].x + v[j].y) + (v[j].z + v[j].w);
+      const float mean2 = warp_sum(s2) * (1.0f / kD);
+      float ss2 = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float a = v[j].x - mean2, b = v[j].y - mean2, c2 = v[j].z - mean2, d = v[j].w - mean2;
+        ss2 += (a * a + b * b) + (c2 * c2 + d * d);
+      }
+      const float rstd2 = rsqrtf(warp_sum(ss2) * (1.0f / kD) + 1e-5f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 g = *reinterpret_cast<const float4*>(g2 + 128 * j + 4 * lane);
+        const float4 b = *reinterpret_cast<const float4*>(b2 + 128 * j + 4 * lane);
+        v[j].x = (v[j].x - mean2) * rstd2 * g.x + b.x;
+        v[j].y = (v[j].y - mean2) * rstd2 * g.y + b.y;
+        v[j].z = (v[j].z - mean2) * rstd2 * g.z + b.z;
+        v[j].w = (v[j].w - mean2) * rstd2 * g.w + b.w;
+      }
+      if (ins.op == OP_HEAD && blockIdx.x == 0) {
+        float* lp = P.cur_latent + (size_t)lrow * kD;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) *reinterpret_cast<float4*>(lp + 128 * j + 4 * lane) = v[j];
+      }
+      if (ins.op == OP_LATENT) {
+        const int drow = P.latent_dst[lrow];
+        if (drow >= 0) {
+          float* lp = P.latent_out + (size_t)drow * kD;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) *reinterpret_cast<float4*>(lp + 128 * j + 4 * lane) = v[j];
+        }
+      }
+    }
+    if (ins.op != OP_LATENT) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<uint2*>(dst + (128 * j + 4 * lane) * 2) =
+            make_uint2(pack_bf16x2(v[j].x, v[j].y), pack_bf16x2(v[j].z, v[j].w));
+    }
+  }
+}
+
+}  // namespace tts

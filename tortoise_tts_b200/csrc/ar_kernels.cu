@@ -1,0 +1,228 @@
+// ar_kernels.cu -- the persistent interpreter kernel (one CTA per SM, cooperative launch) and the small
+// setup kernels (weight repacking, prompt embedding, sampler-state reset).
+#include "ar_gemm.cuh"
+#include "ar_attn.cuh"
+#include "ar_sample.cuh"
+#include "ar_launch.h"
+
+namespace tts {
+
+// ---- the interpreter -------------------------------------------------------------------------------------
+// Warps 0..15: consumers (compute, grid barriers).  Warp 16: producer (weight stream).  The producer is not
+// gated by the grid barriers -- weights do not depend on activations -- so HBM keeps streaming the next
+// stage's (and next layer's, next step's) weights while the consumers wait on a barrier or do attention.
+__global__ void __maxnreg__(120) ar_program_kernel(const __grid_constant__ Params P) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const Smem sm = carve_smem(smem_raw, P.mt_max);
+  Ctrl* c = sm.ctrl;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < P.n_slots; ++i) {
+      mbar_init(&c->full[i], 1);
+      mbar_init(&c->empty[i], kNW);
+    }
+    c->abort_flag = 0;
+    c->stop_flag = 0;
+    c->stop_ci = 0;
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  if (threadIdx.x >= kConsumerThreads) {
+    producer_loop(P, c, sm.ring);
+    return;
+  }
+
+  Pipe pipe;
+  pipe.ci = 0; pipe.slot = 0; pipe.phase = 0; pipe.n_slots = P.n_slots;
+  uint32_t epoch = 0;
+  int steps_done = 0;
+  bool alive = true;
+  for (int step = 0; step < P.n_steps && alive; ++step) {
+    for (int pc = 0; pc < P.n_instr && alive; ++pc) {
+      const Instr ins = P.prog[pc];
+      if (!instr_live(P, step, ins)) continue;
+      if (ins.flags & F_BARRIER_BEFORE) alive = grid_barrier(P, c, epoch);
+      if (!alive) break;
+      if ((ins.flags & F_CHECK_EXIT) && ld_cg_i(P.n_active) == 0) { alive = false; break; }
+      switch (ins.op) {
+        case OP_LN_QKV:
+          if ((ins.flags & F_PLAN) && blockIdx.x == P.G - 1 && (threadIdx.x >> 5) == 0) build_attn_plan(P, P.n_seqs);
+          // fallthrough
+        case OP_PROJ:
+        case OP_LN_FC:
+        case OP_PROJ2:
+        case OP_HEAD: {
+          const int mt = (ins.nrows + 15) >> 4;
+          if (mt <= 1) gemm_stage<1>(P, ins, sm, pipe);
+          else if (mt == 2) gemm_stage<2>(P, ins, sm, pipe);
+          else gemm_stage<4>(P, ins, sm, pipe);
+          break;
+        }
+        case OP_ATTN:
+          attn_stage(P, ins, sm);
+          break;
+        case OP_SAMPLE:
+          sample_stage(P, ins, sm, step);
+          steps_done = step + 1;
+          break;
+        case OP_LATENT: {
+          for (int rg = blockIdx.x; rg * 16 < ins.nrows; rg += P.G) {
+            Instr sub = ins;
+            sub.row0 = ins.row0 + rg * 16;
+            sub.nrows = min(16, ins.nrows - rg * 16);
+            ln_rows_to_smem<true>(P, sub, sm.a_rm, P.lnf_g, P.lnf_b, P.fn_g, P.fn_b, 1);
+          }
+          break;
+        }
+        default: break;
+      }
+      if (c->abort_flag) alive = false;
+    }
+  }
+  consumer_sync();
+  if (threadIdx.x == 0) {
+    if (blockIdx.x == 0) *P.steps_done = steps_done;
+    c->stop_ci = pipe.ci;
+    __threadfence_block();
+    c->stop_flag = 1;
+  }
+}
+
+// ---- weight repacking: HF [K, N] (Conv1D, row-major) or [N, K] (nn.Linear) -> streamed chunk order ----------
+template <typename T>
+__global__ void pack_weight_kernel(const T* __restrict__ src, uint4* __restrict__ dst, int K, int N, int n_tiles,
+                                   int transposed /* 1: src is [N, K] */) {
+  // one thread per 32-bit word (two consecutive k) of the packed image
+  const size_t total_words = (size_t)n_tiles * (K / kChunkK) * (kChunkBytes / 4);
+  uint32_t* out = reinterpret_cast<uint32_t*>(dst);
+  for (size_t wi = (size_t)blockIdx.x * blockDim.x + threadIdx.x; wi < total_words; wi += (size_t)gridDim.x * blockDim.x) {
+    const size_t chunk = wi / (kChunkBytes / 4);
+    const int in_chunk = (int)(wi % (kChunkBytes / 4));
+    const int kq_n = K / kChunkK;
+    const int tile = (int)(chunk / kq_n), kq = (int)(chunk % kq_n);
+    // invert chunk_elem_offset for word `in_chunk` (half = 0)
+    const int word = in_chunk & 3, lane = (in_chunk >> 2) & 31, s = in_chunk >> 7;
+    const int odd = word >> 1, hi = word & 1;
+    const int t = lane & 3, n = lane >> 2;
+    const int kb = 2 * s + odd;
+    const int k = kq * kChunkK + kb * 16 + hi * 8 + 2 * t;
+    const int col = tile * 8 + n;
+    float v0 = 0.f, v1 = 0.f;
+    if (col < N) {
+      if (transposed) {
+        v0 = (float)src[(size_t)col * K + k];
+        v1 = (float)src[(size_t)col * K + k + 1];
+      } else {
+        v0 = (float)src[(size_t)k * N + col];
+        v1 = (float)src[(size_t)(k + 1) * N + col];
+      }
+    }
+    out[wi] = pack_bf16x2(v0, v1);
+  }
+}
+
+template <typename T>
+__global__ void to_f32_kernel(const T* __restrict__ src, float* __restrict__ dst, size_t n, size_t n_pad) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_pad; i += (size_t)gridDim.x * blockDim.x)
+    dst[i] = (i < n) ? (float)src[i] : 0.f;
+}
+
+void launch_pack_weight(const void* src, int dtype, uint4* dst, int K, int N, int n_tiles, int transposed, cudaStream_t st) {
+  const size_t words = (size_t)n_tiles * (K / kChunkK) * (kChunkBytes / 4);
+  const int blocks = (int)((words + 255) / 256 > 4096 ? 4096 : (words + 255) / 256);
+  if (dtype == 0)
+    pack_weight_kernel<float><<<blocks, 256, 0, st>>>((const float*)src, dst, K, N, n_tiles, transposed);
+  else
+    pack_weight_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>((const __nv_bfloat16*)src, dst, K, N, n_tiles, transposed);
+}
+
+void launch_to_f32(const void* src, int dtype, float* dst, size_t n, size_t n_pad, cudaStream_t st) {
+  const int blocks = (int)((n_pad + 255) / 256 > 2048 ? 2048 : (n_pad + 255) / 256);
+  if (dtype == 0)
+    to_f32_kernel<float><<<blocks, 256, 0, st>>>((const float*)src, dst, n, n_pad);
+  else
+    to_f32_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>((const __nv_bfloat16*)src, dst, n, n_pad);
+}
+
+// ---- prompt embedding: rows of every utterance (reference unified_voice.py:639-645 + :203-211) ---------------
+//   row 0: conditioning latent; rows 1..T+2: text_embedding([start, text.., stop]) + text_pos[0..T+1];
+//   mode 0 (inference): last row = mel_embedding(start_mel) + mel_pos[0]
+//   mode 1 (latent re-forward, :577-590): then mel_embedding([start, codes.., stop]) + mel_pos[0..M+1]
+__global__ void embed_rows_kernel(EmbedArgs a) {
+  const int row = blockIdx.x;
+  const int u = a.row_utt[row];
+  const int pos = a.row_pos_in[row];
+  const int T = a.text_len[u];
+  float* xp = a.x + (size_t)row * kD;
+  const float* e0;
+  const float* e1 = nullptr;
+  if (pos == 0) {
+    e0 = a.latent + (size_t)u * kD;
+  } else if (pos <= T + 2) {
+    const int j = pos - 1;
+    int tok = (j == 0) ? a.start_text : (j == T + 1 ? a.stop_text : a.text[(size_t)u * a.text_stride + (j - 1)]);
+    tok = min(max(tok, 0), a.n_text_rows - 1);
+    e0 = a.text_emb + (size_t)tok * kD;
+    e1 = a.text_pos + (size_t)j * kD;
+  } else {
+    const int j = pos - (T + 3);                       // mel position index
+    int tok;
+    if (j == 0) tok = a.start_mel;
+    else if (a.codes && j <= a.codes_len[u]) tok = a.codes[(size_t)u * a.codes_stride + (j - 1)];
+    else tok = a.stop_mel;
+    tok = min(max(tok, 0), a.n_mel_codes - 1);
+    e0 = a.mel_emb + (size_t)tok * kD;
+    e1 = a.mel_pos + (size_t)j * kD;
+  }
+  for (int i = threadIdx.x; i < kD; i += blockDim.x) xp[i] = e0[i] + (e1 ? e1[i] : 0.f);
+}
+
+void launch_embed_rows(const EmbedArgs& a, int n_rows, cudaStream_t st) { embed_rows_kernel<<<n_rows, 256, 0, st>>>(a); }
+
+// ---- sampler state reset after a prompt pass (fake_inputs = [1]*P + [start_mel], unified_voice.py:647-649) ----
+__global__ void reset_sampler_kernel(int n_seqs, int seen_words, uint32_t* seen, int* finished, int* gen_count,
+                                     int* row_pos, int* n_active, int start_mel, int* attn_cnt, int n_cnt) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_seqs * seen_words) {
+    const int wd = i % seen_words;
+    uint32_t v = 0;
+    if (wd == 0) v |= 1u << 1;                         // dummy prompt id 1
+    if (wd == (start_mel >> 5)) v |= 1u << (start_mel & 31);
+    seen[i] = v;
+  }
+  if (i < n_seqs) {
+    finished[i] = 0;
+    gen_count[i] = 0;
+    row_pos[i] = -1;
+  }
+  if (i < n_cnt) attn_cnt[i] = 0;
+  if (i == 0) *n_active = n_seqs;
+}
+
+void launch_reset_sampler(int n_seqs, int seen_words, uint32_t* seen, int* finished, int* gen_count, int* row_pos,
+                          int* n_active, int start_mel, int* attn_cnt, int n_cnt, cudaStream_t st) {
+  int n = n_seqs * seen_words;
+  if (n_cnt > n) n = n_cnt;
+  reset_sampler_kernel<<<(n + 255) / 256, 256, 0, st>>>(n_seqs, seen_words, seen, finished, gen_count, row_pos, n_active,
+                                                        start_mel, attn_cnt, n_cnt);
+}
+
+cudaError_t launch_program(const Params& P, int smem_bytes, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(ar_program_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  void* args[] = {const_cast<Params*>(&P)};
+  return cudaLaunchCooperativeKernel((const void*)ar_program_kernel, dim3(P.G), dim3(kThreads), args, (size_t)smem_bytes, st);
+}
+
+int program_max_ctas_per_sm(int smem_bytes) {
+  int n = 0;
+  cudaFuncSetAttribute(ar_program_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, ar_program_kernel, kThreads, (size_t)smem_bytes);
+  return n;
+}
+
+}  // namespace tts

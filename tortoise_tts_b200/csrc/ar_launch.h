@@ -1,0 +1,31 @@
+// ar_launch.h -- host-callable launchers implemented in ar_kernels.cu.
+#pragma once
+#include <cuda_runtime.h>
+#include "ar_params.h"
+
+namespace tts {
+
+struct EmbedArgs {
+  float* x;
+  const int* row_utt;      // [rows]
+  const int* row_pos_in;   // [rows] position inside the utterance's sequence
+  const int* text_len;     // [utts] (device)
+  const int* text;         // [utts][text_stride]
+  int text_stride;
+  const int* codes;        // nullable [utts][codes_stride] (latent re-forward)
+  const int* codes_len;    // [utts] (device)
+  int codes_stride;
+  const float* latent;     // [utts][1024]
+  const float *text_emb, *text_pos, *mel_emb, *mel_pos;
+  int start_text, stop_text, start_mel, stop_mel, n_text_rows, n_mel_codes;
+};
+
+void launch_pack_weight(const void* src, int dtype, uint4* dst, int K, int N, int n_tiles, int transposed, cudaStream_t st);
+void launch_to_f32(const void* src, int dtype, float* dst, size_t n, size_t n_pad, cudaStream_t st);
+void launch_embed_rows(const EmbedArgs& a, int n_rows, cudaStream_t st);
+void launch_reset_sampler(int n_seqs, int seen_words, uint32_t* seen, int* finished, int* gen_count, int* row_pos,
+                          int* n_active, int start_mel, int* attn_cnt, int n_cnt, cudaStream_t st);
+cudaError_t launch_program(const Params& P, int smem_bytes, cudaStream_t st);
+int program_max_ctas_per_sm(int smem_bytes);
+
+}  // namespace tts

@@ -1,0 +1,129 @@
+// ar_params.h -- structures shared between the host runtime (tts_ar.cu) and the device program
+// interpreter (ar_kernels.cu).  One persistent cooperative kernel executes a small "program" of
+// instructions (one per fused stage of the GPT-2 block) with grid-wide barriers between dependent
+// stages; the same interpreter runs the prompt pass (rows = prompt positions) and the decode loop
+// (rows = live sequences).
+#pragma once
+#include <stdint.h>
+#include <cuda_bf16.h>
+#include "layout.h"
+
+namespace tts {
+
+enum Op : int {
+  OP_LN_QKV = 0,   // x -> ln_1 -> c_attn (+bias) -> q scratch (pre-scaled 1/8) and K/V pages
+  OP_ATTN = 1,     // split-KV attention over the paged cache -> ctx (A-fragment layout)
+  OP_PROJ = 2,     // ctx -> attn.c_proj (+bias) -> x += .
+  OP_LN_FC = 3,    // x -> ln_2 -> c_fc (+bias) -> gelu_new -> h (A-fragment layout)
+  OP_PROJ2 = 4,    // h -> mlp.c_proj (+bias) -> x += .
+  OP_HEAD = 5,     // x -> ln_f -> final_norm -> latent ; -> mel_head (+bias) -> logits
+  OP_SAMPLE = 6,   // logits -> processors/warpers -> token ; next-step embedding
+  OP_LATENT = 7    // x -> ln_f -> final_norm -> out rows (latent re-forward; no GEMM)
+};
+
+enum InstrFlags : int {
+  F_BARRIER_BEFORE = 1,  // grid barrier before executing
+  F_CHECK_EXIT = 2,      // after the barrier: leave the launch if no sequence is unfinished
+  F_ROW_MAP = 4,         // OP_HEAD / OP_LATENT: read x rows through head_rows[]
+  F_PLAN = 8             // OP_LN_QKV of layer 0 in decode: last CTA also builds the attention split plan
+};
+
+struct Instr {
+  int op;
+  int layer;
+  int row0;     // first row (multiple of 16)
+  int nrows;    // rows in this instruction (<= kRowGroup for GEMM ops; all rows for ATTN/SAMPLE/LATENT)
+  int flags;
+  int rot;      // tile-schedule rotation (layout.h tile_range)
+  int pad0, pad1;
+};
+
+struct LayerDev {
+  const uint4 *w_qkv, *w_proj, *w_fc, *w_proj2;            // packed chunks (layout.h)
+  const float *ln1_g, *ln1_b, *ln2_g, *ln2_b;
+  const float *b_qkv, *b_proj, *b_fc, *b_proj2;
+};
+
+struct Params {
+  // geometry
+  int G;                 // CTAs in the grid (== SMs)
+  int n_layers;
+  int V;                 // mel codes (8194)
+  int v_tiles;           // ceil(V / 8)
+  int v_stride;          // logits row stride (floats)
+  int n_slots;           // ring slots of kChunkBytes
+  int mt_max;            // largest M-tile count any instruction uses (sizes the A staging area)
+  int decode_mode;       // 1: rows are sequences (private pages); 0: rows are prompt positions
+  // weights
+  const LayerDev* layers;
+  const uint4* w_head;
+  const float *b_head, *lnf_g, *lnf_b, *fn_g, *fn_b;
+  const float *mel_emb, *mel_pos;
+  // activations (row-indexed)
+  float* x;              // [rows][1024] residual stream, fp32
+  float* q;              // [rows][1024] query, pre-scaled by 1/sqrt(64)
+  __nv_bfloat16* ctx;    // A-fragment layout, K = 1024
+  __nv_bfloat16* hbuf;   // A-fragment layout, K = 4096
+  float* logits;         // [logit rows][v_stride]
+  float* cur_latent;     // [logit rows][1024] final_norm(ln_f(x)) of the rows fed to the head
+  // KV cache
+  __nv_bfloat16* kv;     // page pool (layout.h kv_row_offset)
+  int n_pages;
+  const int* prefix_pt;  // [utts][kMaxPagesPerSeg]
+  const int* priv_pt;    // [seqs][kMaxPagesPerSeg]
+  const int* utt_plen;   // [utts] prompt length P+1
+  int* row_utt;          // [rows] utterance of each row
+  int* row_pos;          // [rows] position of the row's token in its sequence; -1 = inactive row
+  const int* head_rows;  // [logit rows] row map for F_ROW_MAP
+  // attention scratch
+  float* part;           // [units][kPartStride]
+  int* attn_cnt;         // [rows * 16] arrival counters (zero between uses)
+  int* plan;             // [0]=mode(0 direct,1 split) [1]=n_units [2]=tp ; [4 + r]=unit_off[r] (rows+1 entries)
+  int plan_cap_units;
+  // sampler state (per sequence)
+  int* finished;
+  int* gen_count;        // tokens generated so far
+  uint32_t* seen;        // [seqs][seen_words] repetition-penalty id set
+  int seen_words;
+  int* n_active;         // unfinished sequences
+  const int* seq_utt;
+  int first_step_from_prefill;  // 1: the first SAMPLE of this launch reads logits row seq_utt[s]
+  int n_seqs;
+  // sampler config
+  int do_sample, top_k, ignore_eos;
+  float temperature, top_p, rep_penalty;
+  unsigned long long seed;
+  long long seq_index_base;
+  int stop_token;
+  int max_pos_rows;      // rows of mel_pos (bounds guard)
+  // outputs
+  long long* out_codes;  // [seqs][out_stride], column = step index within this launch
+  int out_stride;
+  float* out_latents;    // nullable [seqs][out_stride][1024]
+  const int* forced;     // nullable [seqs][out_stride]
+  int* out_choice;       // nullable [seqs][out_stride]
+  float* latent_out;     // OP_LATENT destination rows [n][1024] via latent_dst
+  const int* latent_dst; // [rows] destination row index in latent_out or -1
+  // control
+  unsigned int* bar_counter;
+  int* watchdog;
+  int* steps_done;
+  const Instr* prog;
+  int n_instr;
+  int n_steps;
+  int skip_last_model;   // generate(): the model is not run after the last sampled token
+};
+
+// dynamic shared memory layout of the interpreter kernel
+constexpr int kSmemCtrlBytes = 1024;
+constexpr int kSmemRedBytes = 33792;                     // >= 16 warps * 4 tiles * 512 B, >= V floats
+TTS_HD int smem_a_bytes(int mt_max) { return mt_max * 16 * kARowBytes; }
+TTS_HD int smem_total_bytes(int mt_max, int n_slots) {
+  return kSmemCtrlBytes + smem_a_bytes(mt_max) + kSmemRedBytes + n_slots * kChunkBytes;
+}
+TTS_HD int smem_max_slots(int mt_max, int budget) {
+  int s = (budget - kSmemCtrlBytes - smem_a_bytes(mt_max) - kSmemRedBytes) / kChunkBytes;
+  return s > 12 ? 12 : s;
+}
+
+}  // namespace tts

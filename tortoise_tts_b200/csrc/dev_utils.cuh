@@ -1,0 +1,176 @@
+// dev_utils.cuh -- sm_100a PTX wrappers: mbarrier, 1-D bulk (TMA engine) copies, ldmatrix / mma,
+// cache-controlled loads, a watchdogged grid barrier, Philox4x32-10 and block reductions.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include "layout.h"
+
+namespace tts {
+
+// Every device-side wait is bounded: a hung GPU box is a strike (no progress for ~2 s => give up,
+// raise the watchdog flag, let every CTA fall through to the end of the kernel).
+constexpr long long kWatchdogCycles = 4000000000LL;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+// ---- mbarrier -----------------------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Returns false on watchdog expiry (or when *abort_flag is set by someone else).
+__device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, volatile int* abort_flag) {
+  if (mbar_try_wait(bar, parity)) return true;
+  long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > kWatchdogCycles || *abort_flag) {
+      *abort_flag = 1;
+      return false;
+    }
+  }
+  return true;
+}
+
+// ---- bulk async copy global -> shared (UBLKCP), completion on an mbarrier ---------------------------------
+__device__ __forceinline__ uint64_t make_evict_first_policy() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+          smem_u32(dst_smem)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+      : "memory");
+}
+
+// ---- loads that must see other CTAs' writes (activations, KV written this launch): L2 only -----------------
+__device__ __forceinline__ uint4 ld_cg_u4(const void* p) { return __ldcg(reinterpret_cast<const uint4*>(p)); }
+__device__ __forceinline__ float4 ld_cg_f4(const void* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ float2 ld_cg_f2(const void* p) { return __ldcg(reinterpret_cast<const float2*>(p)); }
+__device__ __forceinline__ float ld_cg_f(const float* p) { return __ldcg(p); }
+__device__ __forceinline__ int ld_cg_i(const int* p) { return __ldcg(p); }
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_add_u32(uint32_t* p, uint32_t v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// ---- tensor core (legacy warp-level path; the dense contractions use tcgen05, see gemm_tc.cu) -----------
+__device__ __forceinline__ void ldmatrix_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+               : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint4& a, uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
+
+// ---- named barrier over the consumer warps only (the producer warp never joins) ------------------------------
+__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumerThreads) : "memory"); }
+
+// ---- warp / block reductions (fixed trees: deterministic) -------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+// 512 consumer threads; `scratch` = 32 floats of shared memory.  All consumer threads must call.
+__device__ __forceinline__ float block_sum(float v, float* scratch) {
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  v = warp_sum(v);
+  consumer_sync();
+  if (lane == 0) scratch[w] = v;
+  consumer_sync();
+  float r = (lane < kNW) ? scratch[lane] : 0.f;
+  return warp_sum(r);
+}
+__device__ __forceinline__ float block_max(float v, float* scratch) {
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  v = warp_max(v);
+  consumer_sync();
+  if (lane == 0) scratch[w] = v;
+  consumer_sync();
+  float r = (lane < kNW) ? scratch[lane] : -INFINITY;
+  return warp_max(r);
+}
+__device__ __forceinline__ uint32_t block_sum_u32(uint32_t v, float* scratch) {
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  v = __reduce_add_sync(0xffffffffu, v);
+  consumer_sync();
+  if (lane == 0) reinterpret_cast<uint32_t*>(scratch)[w] = v;
+  consumer_sync();
+  uint32_t r = (lane < kNW) ? reinterpret_cast<uint32_t*>(scratch)[lane] : 0u;
+  return __reduce_add_sync(0xffffffffu, r);
+}
+
+// ---- Philox4x32-10 (oracle/philox.py is the checked definition) --------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+    uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+    k.x += 0x9E3779B9u;
+    k.y += 0xBB67AE85u;
+  }
+  return c;
+}
+__device__ __forceinline__ float philox_uniform(uint64_t seed, uint32_t seq_index, uint32_t step) {
+  uint4 r = philox4x32_10(make_uint4(seq_index, step, 0u, 0u), make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+  return (float)(r.x >> 8) * (1.0f / 16777216.0f);
+}
+
+__device__ __forceinline__ float gelu_new(float x) {
+  // HF NewGELUActivation: 0.5 x (1 + tanh( sqrt(2/pi) (x + 0.044715 x^3) ))
+  float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
+  return 0.5f * x * (1.0f + tanhf(u));
+}
+
+}  // namespace tts

@@ -1,0 +1,89 @@
+// tts_ar_host.h -- host-side state behind the opaque TtsArHandle (tts_ar.cu, tts_ar_run.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <string>
+#include <vector>
+#include "../../include/tts_ar.h"
+#include "ar_launch.h"
+
+struct TtsArHandle {
+  TtsArConfig cfg{};
+  int G = 0;                 // CTAs == SMs
+  int smem_budget = 0;       // opt-in dynamic shared memory per CTA
+  std::string err;
+  std::vector<void*> allocs; // everything cudaMalloc'ed, freed in destroy
+
+  // capacity
+  int plen_max = 0;          // max prompt length P+1 = text + 4
+  int rows_cap = 0;          // activation rows
+  int npp = 0, nqp = 0;      // pages per prompt / per private segment
+  int n_pages = 0;
+  int rf_rows_cap = 0;       // rows per latent re-forward sub-batch
+  int logit_rows_cap = 0;
+  int plan_cap_units = 0;
+  int seen_words = 0;
+  int v_tiles = 0, v_stride = 0;
+
+  // weights (device)
+  bool weights_loaded = false;
+  std::vector<tts::LayerDev> layers_host;
+  tts::LayerDev* d_layers = nullptr;
+  uint4* d_warena = nullptr;
+  float* d_fparams = nullptr;       // LN gains/biases, linear biases (fp32)
+  uint4* d_w_head = nullptr;
+  float *d_b_head = nullptr, *d_lnf_g = nullptr, *d_lnf_b = nullptr, *d_fn_g = nullptr, *d_fn_b = nullptr;
+  float *d_mel_emb = nullptr, *d_mel_pos = nullptr, *d_text_emb = nullptr, *d_text_pos = nullptr;
+
+  // activations / cache (device)
+  float *d_x = nullptr, *d_q = nullptr, *d_logits = nullptr, *d_cur_latent = nullptr, *d_part = nullptr;
+  __nv_bfloat16 *d_ctx = nullptr, *d_h = nullptr, *d_kv = nullptr;
+  int *d_prefix_pt = nullptr, *d_priv_pt = nullptr, *d_utt_plen = nullptr;
+  int *d_pf_row_utt = nullptr, *d_pf_row_pos = nullptr, *d_head_rows = nullptr, *d_latent_dst = nullptr;
+  int *d_seq_utt = nullptr, *d_seq_pos = nullptr;
+  int *d_attn_cnt = nullptr, *d_plan = nullptr;
+  int *d_finished = nullptr, *d_gen_count = nullptr, *d_n_active = nullptr;
+  uint32_t* d_seen = nullptr;
+  int *d_text_len = nullptr, *d_codes_len = nullptr;
+  unsigned int* d_bar = nullptr;
+  int *d_watchdog = nullptr, *d_steps_done = nullptr;
+  tts::Instr *d_prog_pf = nullptr, *d_prog_dec = nullptr;
+  int prog_pf_cap = 0, prog_dec_cap = 0;
+  // staging for the host-buffer entry point (pinned host + device)
+  float* d_in_latent = nullptr;
+  int* d_in_text = nullptr;
+  long long* d_out_codes = nullptr;
+  int *h_pinned_i = nullptr;     // pinned int scratch: [0]=steps_done [1]=watchdog
+  long long* h_pinned_codes = nullptr;
+  float* h_pinned_latent = nullptr;
+  int* h_pinned_text = nullptr;
+
+  // per-call state
+  bool prefilled = false;
+  int n_utt = 0, n_cand = 0, n_seqs = 0;
+  std::vector<int> plen;        // per utterance P+1
+  int tokens_done = 0;          // tokens sampled so far for the current prompt
+  bool first_step_pending = false;
+  int dec_n_instr = 0, dec_mt_max = 1, pf_n_instr = 0, pt_rows = 0;
+  long long launches = 0;
+  double last_bytes = 0.0;
+  int last_model_passes = 0;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+  bool timing_valid = false;
+};
+
+namespace tts {
+int fail(TtsArHandle* h, int code, const std::string& msg);
+int cuda_fail(TtsArHandle* h, cudaError_t e, const char* what);
+// builds + uploads the decode program for h->n_seqs sequences; fills the Params fields it owns
+int build_decode_program(TtsArHandle* h, cudaStream_t st);
+void fill_common_params(TtsArHandle* h, Params& P);
+int run_prompt_pass(TtsArHandle* h, const std::vector<int>& seq_len, const std::vector<int>& row_utt,
+                    const std::vector<int>& row_pos, const std::vector<int>& head_rows, const std::vector<int>& latent_dst,
+                    float* latent_out, bool with_head, cudaStream_t st);
+}  // namespace tts
+
+#define TTS_CUDA(h, call)                                          \
+  do {                                                             \
+    cudaError_t e__ = (call);                                      \
+    if (e__ != cudaSuccess) return tts::cuda_fail((h), e__, #call); \
+  } while (0)

@@ -1,0 +1,421 @@
+// tts_ar_run.cu -- C ABI call path: prompt pass, sample loop, latent re-forward, host-buffer entry.
+#include <cstdio>
+#include <cstring>
+#include <algorithm>
+#include "tts_ar_host.h"
+
+using namespace tts;
+
+namespace tts {
+
+void fill_common_params(TtsArHandle* h, Params& P) {
+  memset(&P, 0, sizeof(P));
+  const TtsArConfig& c = h->cfg;
+  P.G = h->G;
+  P.n_layers = c.n_layers;
+  P.V = c.n_mel_codes;
+  P.v_tiles = h->v_tiles;
+  P.v_stride = h->v_stride;
+  P.layers = h->d_layers;
+  P.w_head = h->d_w_head;
+  P.b_head = h->d_b_head;
+  P.lnf_g = h->d_lnf_g; P.lnf_b = h->d_lnf_b; P.fn_g = h->d_fn_g; P.fn_b = h->d_fn_b;
+  P.mel_emb = h->d_mel_emb; P.mel_pos = h->d_mel_pos;
+  P.x = h->d_x; P.q = h->d_q; P.ctx = h->d_ctx; P.hbuf = h->d_h;
+  P.logits = h->d_logits; P.cur_latent = h->d_cur_latent;
+  P.kv = h->d_kv; P.n_pages = h->n_pages;
+  P.prefix_pt = h->d_prefix_pt; P.priv_pt = h->d_priv_pt; P.utt_plen = h->d_utt_plen;
+  P.head_rows = h->d_head_rows;
+  P.part = h->d_part; P.attn_cnt = h->d_attn_cnt; P.plan = h->d_plan; P.plan_cap_units = h->plan_cap_units;
+  P.finished = h->d_finished; P.gen_count = h->d_gen_count; P.seen = h->d_seen; P.seen_words = h->seen_words;
+  P.n_active = h->d_n_active; P.seq_utt = h->d_seq_utt;
+  P.stop_token = c.stop_mel_token;
+  P.max_pos_rows = c.n_mel_pos;
+  P.latent_dst = h->d_latent_dst;
+  P.bar_counter = h->d_bar; P.watchdog = h->d_watchdog; P.steps_done = h->d_steps_done;
+}
+
+static void push_gemm_groups(std::vector<Instr>& prog, int op, int layer, int n_rows, int rot, int first_flags) {
+  for (int r0 = 0, g = 0; r0 < n_rows; r0 += kRowGroup, ++g) {
+    Instr in{};
+    in.op = op; in.layer = layer; in.row0 = r0; in.nrows = std::min(kRowGroup, n_rows - r0);
+    in.flags = (g == 0) ? first_flags : 0;
+    in.rot = rot;
+    prog.push_back(in);
+  }
+}
+
+// One pass over all layers for `n_rows` rows; `rot` carries the tile-schedule rotation across GEMMs.
+static void push_layers(std::vector<Instr>& prog, int n_layers, int n_rows, int G, int& rot, int first_qkv_flags) {
+  for (int l = 0; l < n_layers; ++l) {
+    push_gemm_groups(prog, OP_LN_QKV, l, n_rows, rot, F_BARRIER_BEFORE | (l == 0 ? first_qkv_flags : 0));
+    rot = next_rot(kD3 / 8, G, rot);
+    Instr at{};
+    at.op = OP_ATTN; at.layer = l; at.row0 = 0; at.nrows = n_rows; at.flags = F_BARRIER_BEFORE;
+    prog.push_back(at);
+    push_gemm_groups(prog, OP_PROJ, l, n_rows, rot, F_BARRIER_BEFORE);
+    rot = next_rot(kD / 8, G, rot);
+    push_gemm_groups(prog, OP_LN_FC, l, n_rows, rot, F_BARRIER_BEFORE);
+    rot = next_rot(kD4 / 8, G, rot);
+    push_gemm_groups(prog, OP_PROJ2, l, n_rows, rot, F_BARRIER_BEFORE);
+    rot = next_rot(kD / 8, G, rot);
+  }
+}
+
+static int mt_max_for(int n_rows) {
+  const int m = (std::min(n_rows, kRowGroup) + 15) / 16;
+  return m <= 1 ? 1 : (m == 2 ? 2 : 4);
+}
+
+int build_decode_program(TtsArHandle* h, cudaStream_t st) {
+  std::vector<Instr> prog;
+  Instr s{};
+  s.op = OP_SAMPLE; s.nrows = h->n_seqs; s.flags = F_BARRIER_BEFORE;
+  prog.push_back(s);
+  int rot = 0;
+  push_layers(prog, h->cfg.n_layers, h->n_seqs, h->G, rot, F_CHECK_EXIT | F_PLAN);
+  push_gemm_groups(prog, OP_HEAD, 0, h->n_seqs, rot, F_BARRIER_BEFORE);
+  if ((int)prog.size() > h->prog_dec_cap) return fail(h, TTS_AR_ERR_CAPACITY, "decode program too long");
+  h->dec_n_instr = (int)prog.size();
+  h->dec_mt_max = mt_max_for(h->n_seqs);
+  TTS_CUDA(h, cudaMemcpyAsync(h->d_prog_dec, prog.data(), sizeof(Instr) * prog.size(), cudaMemcpyHostToDevice, st));
+  TTS_CUDA(h, cudaStreamSynchronize(st));   // `prog` is a local pageable buffer
+  return 0;
+}
+
+static int launch(TtsArHandle* h, Params& P, cudaStream_t st) {
+  P.n_slots = smem_max_slots(P.mt_max, h->smem_budget);
+  if (P.n_slots < 2) return fail(h, TTS_AR_ERR_DEVICE, "not enough shared memory for the weight ring");
+  TTS_CUDA(h, cudaMemsetAsync(h->d_bar, 0, sizeof(unsigned int), st));
+  cudaError_t e = launch_program(P, smem_total_bytes(P.mt_max, P.n_slots), st);
+  if (e != cudaSuccess) return cuda_fail(h, e, "cudaLaunchCooperativeKernel(ar_program_kernel)");
+  h->launches += 1;
+  return 0;
+}
+
+// Prompt-shaped causal pass: sequences laid out back to back as rows; every sequence is its own "utterance"
+// whose KV lives in prefix pages.  Used by tts_ar_prefill (with_head) and tts_ar_forward_latents (latent_out).
+int run_prompt_pass(TtsArHandle* h, const std::vector<int>& seq_len, const std::vector<int>& row_utt,
+                    const std::vector<int>& row_pos, const std::vector<int>& head_rows, const std::vector<int>& latent_dst,
+                    float* latent_out, bool with_head, cudaStream_t st) {
+  const int n_seq = (int)seq_len.size();
+  const int n_rows = (int)row_utt.size();
+  if (n_rows > h->rows_cap) return fail(h, TTS_AR_ERR_CAPACITY, "prompt rows exceed capacity");
+  // page tables: sequence i owns pages [base_i, base_i + ceil(len/32))
+  std::vector<int> pt((size_t)n_seq * kMaxPagesPerSeg, 0);
+  int next_page = 0;
+  for (int i = 0; i < n_seq; ++i) {
+    const int np = (seq_len[i] + kPage - 1) / kPage;
+    if (np > kMaxPagesPerSeg) return fail(h, TTS_AR_ERR_CAPACITY, "sequence longer than 1024 positions");
+    for (int p = 0; p < np; ++p) pt[(size_t)i * kMaxPagesPerSeg + p] = next_page++;
+  }
+  if (next_page > h->n_pages) return fail(h, TTS_AR_ERR_CAPACITY, "KV page pool exhausted");
+  std::vector<Instr> prog;
+  int rot = 0;
+  push_layers(prog, h->cfg.n_layers, n_rows, h->G, rot, 0);
+  int n_head_rows = 0;
+  if (with_head) {
+    n_head_rows = (int)head_rows.size();
+    for (int r0 = 0, g = 0; r0 < n_head_rows; r0 += kRowGroup, ++g) {
+      Instr in{};
+      in.op = OP_HEAD; in.row0 = r0; in.nrows = std::min(kRowGroup, n_head_rows - r0);
+      in.flags = F_ROW_MAP | (g == 0 ? F_BARRIER_BEFORE : 0);
+      in.rot = rot;
+      prog.push_back(in);
+    }
+  } else {
+    Instr in{};
+    in.op = OP_LATENT; in.row0 = 0; in.nrows = n_rows; in.flags = F_BARRIER_BEFORE;
+    prog.push_back(in);
+  }
+  if ((int)prog.size() > h->prog_pf_cap) return fail(h, TTS_AR_ERR_CAPACITY, "prompt program too long");
+  h->pf_n_instr = (int)prog.size();
+  TTS_CUDA(h, cudaMemcpyAsync(h->d_prefix_pt, pt.data(), sizeof(int) * pt.size(), cudaMemcpyHostToDevice, st));
+  TTS_CUDA(h, cudaMemcpyAsync(h->d_utt_plen, seq_len.data(), sizeof(int) * n_seq, cudaMemcpyHostToDevice, st));
+  TTS_CUDA(h, cudaMemcpyAsync(h->d_pf_row_utt, row_utt.data(), sizeof(int) * n_rows, cudaMemcpyHostToDevice, st));
+  TTS_CUDA(h, cudaMemcpyAsync(h->d_pf_row_pos, row_pos.data(), sizeof(int) * n_rows, cudaMemcpyHostToDevice, st));
+  if (with_head)
+    TTS_CUDA(h, cudaMemcpyAsync(h->d_head_rows, head_rows.data(), sizeof(int) * n_head_rows, cudaMemcpyHostToDevice, st));
+  else
+    TTS_CUDA(h, cudaMemcpyAsync(h->d_latent_dst, latent_dst.data(), sizeof(int) * n_rows, cudaMemcpyHostToDevice, st));
+  TTS_CUDA(h, cudaMemcpyAsync(h->d_prog_pf, prog.data(), sizeof(Instr) * prog.size(), cudaMemcpyHostToDevice, st));
+  TTS_CUDA(h, cudaMemsetAsync(h->d_plan, 0, sizeof(int) * 4, st));   // plan[0] = 0: direct (row, head) units
+  TTS_CUDA(h, cudaStreamSynchronize(st));                             // local pageable buffers above
+  return 0;
+}
+
+}  // namespace tts
+
+static int check_ready(TtsArHandle* h, bool need_prefill) {
+  if (!h) return TTS_AR_ERR_BAD_ARG;
+  if (!h->weights_loaded) return fail(h, TTS_AR_ERR_STATE, "tts_ar_load_weights has not been called");
+  if (need_prefill && !h->prefilled) return fail(h, TTS_AR_ERR_STATE, "tts_ar_prefill has not been called");
+  cudaError_t e = cudaSetDevice(h->cfg.device);
+  if (e != cudaSuccess) return cuda_fail(h, e, "cudaSetDevice");
+  return 0;
+}
+
+extern "C" int tts_ar_prefill(TtsArHandle* h, const float* latent, const int32_t* text, int32_t text_stride,
+                              const int32_t* text_len, int32_t n_utt, int32_t n_cand, void* stream) {
+  int rc = check_ready(h, false);
+  if (rc) return rc;
+  if (!latent || !text || !text_len || n_utt < 1 || n_cand < 1) return fail(h, TTS_AR_ERR_BAD_ARG, "bad prefill argument");
+  const TtsArConfig& c = h->cfg;
+  if (n_utt > c.max_utts || n_utt * n_cand > c.max_seqs) return fail(h, TTS_AR_ERR_CAPACITY, "batch exceeds max_utts / max_seqs");
+  cudaStream_t st = (cudaStream_t)stream;
+  std::vector<int> seq_len(n_utt), row_utt, row_pos, head_rows(n_utt), none;
+  for (int u = 0; u < n_utt; ++u) {
+    if (text_len[u] < 0 || text_len[u] > c.max_text_len || text_len[u] > text_stride)
+      return fail(h, TTS_AR_ERR_CAPACITY, "text length exceeds max_text_len / text_stride");
+    seq_len[u] = text_len[u] + 4;          // latent + start_text + text + stop_text + start_mel
+    for (int p = 0; p < seq_len[u]; ++p) { row_utt.push_back(u); row_pos.push_back(p); }
+    head_rows[u] = (int)row_utt.size() - 1;
+  }
+  const int n_rows = (int)row_utt.size();
+  h->prefilled = false;
+  TTS_CUDA(h, cudaEventRecord(h->ev0, st));
+  TTS_CUDA(h, cudaMemcpyAsync(h->d_text_len, text_len, sizeof(int) * n_utt, cudaMemcpyHostToDevice, st));
+  rc = run_prompt_pass(h, seq_len, row_utt, row_pos, head_rows, none, nullptr, true, st);
+  if (rc) return rc;
+  EmbedArgs ea{};
+  ea.x = h->d_x; ea.row_utt = h->d_pf_row_utt; ea.row_pos_in = h->d_pf_row_pos; ea.text_len = h->d_text_len;
+  ea.text = text; ea.text_stride = text_stride; ea.codes = nullptr; ea.codes_len = h->d_codes_len; ea.codes_stride = 0;
+  ea.latent = latent; ea.text_emb = h->d_text_emb; ea.text_pos = h->d_text_pos; ea.mel_emb = h->d_mel_emb; ea.mel_pos = h->d_mel_pos;
+  ea.start_text = c.start_text_token; ea.stop_text = c.stop_text_token; ea.start_mel = c.start_mel_token; ea.stop_mel = c.stop_mel_token;
+  ea.n_text_rows = c.n_text_rows; ea.n_mel_codes = c.n_mel_codes;
+  launch_embed_rows(ea, n_rows, st);
+  h->launches += 1;
+  Params P;
+  fill_common_params(h, P);
+  P.decode_mode = 0;
+  P.row_utt = h->d_pf_row_utt; P.row_pos = h->d_pf_row_pos;
+  P.mt_max = mt_max_for(std::max(n_rows, n_utt));
+  P.prog = h->d_prog_pf;
+  P.n_instr = h->pf_n_instr;
+  P.n_steps = 1;
+  P.n_seqs = 0;
+  rc = launch(h, P, st);
+  if (rc) return rc;
+  // sequences: utterance-major, candidates adjacent (repeat_interleave, stream_generator.py:618-623)
+  h->n_utt = n_utt; h->n_cand = n_cand; h->n_seqs = n_utt * n_cand;
+  h->plen = seq_len;
+  std::vector<int> seq_utt(h->n_seqs), priv((size_t)h->n_seqs * kMaxPagesPerSeg, 0);
+  int next_page = 0;
+  for (int u = 0; u < n_utt; ++u) next_page += (seq_len[u] + kPage - 1) / kPage;
+  for (int s = 0; s < h->n_seqs; ++s) {
+    seq_utt[s] = s / n_cand;
+    for (int p = 0; p < h->nqp; ++p) priv[(size_t)s * kMaxPagesPerSeg + p] = next_page++;
+  }
+  if (next_page > h->n_pages) return fail(h, TTS_AR_ERR_CAPACITY, "KV page pool exhausted");
+  TTS_CUDA(h, cudaMemcpyAsync(h->d_seq_utt, seq_utt.data(), sizeof(int) * h->n_seqs, cudaMemcpyHostToDevice, st));
+  TTS_CUDA(h, cudaMemcpyAsync(h->d_priv_pt, priv.data(), sizeof(int) * priv.size(), cudaMemcpyHostToDevice, st));
+  launch_reset_sampler(h->n_seqs, h->seen_words, h->d_seen, h->d_finished, h->d_gen_count, h->d_seq_pos, h->d_n_active,
+                       c.start_mel_token, h->d_attn_cnt, h->n_seqs * kH, st);
+  h->launches += 1;
+  rc = build_decode_program(h, st);   // synchronises: seq_utt / priv are local
+  if (rc) return rc;
+  TTS_CUDA(h, cudaEventRecord(h->ev1, st));
+  TTS_CUDA(h, cudaGetLastError());
+  h->tokens_done = 0;
+  h->first_step_pending = true;
+  h->prefilled = true;
+  h->timing_valid = false;
+  return 0;
+}
+
+static int run_steps(TtsArHandle* h, const TtsArSampling* s, int n_steps, bool skip_last_model, long long* out_codes,
+                     float* out_latents, const int32_t* forced, int32_t* out_choice, cudaStream_t st) {
+  const TtsArConfig& c = h->cfg;
+  if (!s || s->struct_size != (int)sizeof(TtsArSampling)) return fail(h, TTS_AR_ERR_BAD_ARG, "TtsArSampling.struct_size mismatch");
+  if (!out_codes || n_steps < 1) return fail(h, TTS_AR_ERR_BAD_ARG, "bad generate argument");
+  if (s->do_sample && !(s->temperature > 0.f)) return fail(h, TTS_AR_ERR_BAD_ARG, "temperature must be > 0");
+  if (s->do_sample && !(s->top_p > 0.f)) return fail(h, TTS_AR_ERR_BAD_ARG, "top_p must be > 0");
+  if (!(s->repetition_penalty > 0.f)) return fail(h, TTS_AR_ERR_BAD_ARG, "repetition_penalty must be > 0");
+  // the model is run (n_steps - skip) more times: positions / mel_pos rows must exist for every fed token
+  const int fed = h->tokens_done + n_steps - (skip_last_model ? 1 : 0);
+  if (fed > c.max_new_tokens || fed + 1 >= c.n_mel_pos) return fail(h, TTS_AR_ERR_CAPACITY, "generation length exceeds max_new_tokens");
+  Params P;
+  fill_common_params(h, P);
+  P.decode_mode = 1;
+  P.row_utt = h->d_seq_utt; P.row_pos = h->d_seq_pos;
+  P.mt_max = h->dec_mt_max;
+  P.prog = h->d_prog_dec; P.n_instr = h->dec_n_instr;
+  P.n_steps = n_steps; P.skip_last_model = skip_last_model ? 1 : 0;
+  P.n_seqs = h->n_seqs;
+  P.first_step_from_prefill = h->first_step_pending ? 1 : 0;
+  P.do_sample = s->do_sample; P.top_k = s->top_k; P.ignore_eos = s->ignore_eos;
+  P.temperature = s->temperature; P.top_p = s->top_p; P.rep_penalty = s->repetition_penalty;
+  P.seed = s->seed; P.seq_index_base = s->seq_index_base;
+  P.out_codes = out_codes; P.out_stride = n_steps; P.out_latents = out_latents; P.forced = forced; P.out_choice = out_choice;
+  int rc = launch(h, P, st);
+  if (rc) return rc;
+  // SURVEY.md 8(d) algorithmic bytes, assuming every sequence stays live (exact under ignore_eos)
+  const double W = 2.0 * ((double)c.n_layers * 12596224.0 + 4096.0 + (double)c.n_mel_codes * (kD + 1));
+  const double kappa = (double)c.n_layers * 2 * kD * 2;
+  double prompt = 0;
+  for (int u = 0; u < h->n_utt; ++u) prompt += h->plen[u] * kappa;
+  double bytes = 0;
+  const int passes = n_steps - (skip_last_model ? 1 : 0);
+  for (int k = 0; k < passes; ++k) bytes += W + 4096.0 * h->n_seqs + prompt + (double)h->n_seqs * (h->tokens_done + k + 1) * kappa;
+  h->last_bytes = bytes;
+  h->last_model_passes = passes;
+  h->tokens_done += n_steps;
+  h->first_step_pending = false;
+  TTS_CUDA(h, cudaEventRecord(h->ev2, st));
+  h->timing_valid = true;
+  return 0;
+}
+
+extern "C" int tts_ar_generate(TtsArHandle* h, const TtsArSampling* s, int32_t max_new, int64_t* out_codes,
+                               float* out_latents, const int32_t* forced, int32_t* out_choice, void* stream) {
+  int rc = check_ready(h, true);
+  if (rc) return rc;
+  if (!h->first_step_pending) return fail(h, TTS_AR_ERR_STATE, "tts_ar_generate needs a fresh tts_ar_prefill");
+  return run_steps(h, s, max_new, true, (long long*)out_codes, out_latents, forced, out_choice, (cudaStream_t)stream);
+}
+
+extern "C" int tts_ar_step(TtsArHandle* h, const TtsArSampling* s, int32_t n_steps, int64_t* out_codes,
+                           float* out_latents, const int32_t* forced, int32_t* out_choice, void* stream) {
+  int rc = check_ready(h, true);
+  if (rc) return rc;
+  return run_steps(h, s, n_steps, false, (long long*)out_codes, out_latents, forced, out_choice, (cudaStream_t)stream);
+}
+
+extern "C" int tts_ar_logits_debug(TtsArHandle* h, float* out, int32_t* rows_out, void* stream) {
+  int rc = check_ready(h, true);
+  if (rc) return rc;
+  if (!out) return fail(h, TTS_AR_ERR_BAD_ARG, "null argument");
+  const int rows = h->first_step_pending ? h->n_utt : h->n_seqs;
+  TTS_CUDA(h, cudaMemcpy2DAsync(out, sizeof(float) * h->cfg.n_mel_codes, h->d_logits, sizeof(float) * h->v_stride,
+                                sizeof(float) * h->cfg.n_mel_codes, rows, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  if (rows_out) *rows_out = rows;
+  return 0;
+}
+
+extern "C" int tts_ar_sync_result(TtsArHandle* h, TtsArStats* out, void* stream) {
+  if (!h || !out) return TTS_AR_ERR_BAD_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  TTS_CUDA(h, cudaSetDevice(h->cfg.device));
+  TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[0], h->d_steps_done, sizeof(int), cudaMemcpyDeviceToHost, st));
+  TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[1], h->d_watchdog, sizeof(int), cudaMemcpyDeviceToHost, st));
+  TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[2], h->d_n_active, sizeof(int), cudaMemcpyDeviceToHost, st));
+  TTS_CUDA(h, cudaStreamSynchronize(st));
+  memset(out, 0, sizeof(*out));
+  out->struct_size = (int)sizeof(TtsArStats);
+  out->steps_run = h->h_pinned_i[0];
+  out->watchdog = h->h_pinned_i[1];
+  out->all_finished = h->h_pinned_i[2] == 0;
+  out->kernel_launches = h->launches;
+  out->last_algorithmic_bytes = h->last_bytes;
+  if (h->timing_valid) {
+    float a = 0.f, b = 0.f;
+    if (cudaEventElapsedTime(&a, h->ev0, h->ev1) == cudaSuccess) out->last_prefill_ms = a;
+    if (cudaEventElapsedTime(&b, h->ev0, h->ev2) == cudaSuccess) out->last_device_ms = b;
+    cudaGetLastError();
+  }
+  if (out->watchdog) return fail(h, TTS_AR_ERR_WATCHDOG, "device-side wait timed out (watchdog); results are invalid");
+  return 0;
+}
+
+extern "C" int tts_ar_forward_latents(TtsArHandle* h, const float* latent, const int32_t* text, int32_t text_stride,
+                                      const int32_t* text_len, const int32_t* codes, int32_t codes_stride,
+                                      const int32_t* codes_len, int32_t n, float* out, void* stream) {
+  int rc = check_ready(h, false);
+  if (rc) return rc;
+  if (!latent || !text || !text_len || !codes || !codes_len || !out || n < 1) return fail(h, TTS_AR_ERR_BAD_ARG, "bad forward_latents argument");
+  const TtsArConfig& c = h->cfg;
+  cudaStream_t st = (cudaStream_t)stream;
+  h->prefilled = false;   // the KV pool and activations are reused: generation state is gone
+  int i0 = 0;
+  while (i0 < n) {
+    // sub-batch that fits the row capacity
+    int i1 = i0, rows = 0, pages = 0;
+    while (i1 < n) {
+      if (text_len[i1] < 0 || text_len[i1] > c.max_text_len || codes_len[i1] < 0 || codes_len[i1] + 2 > c.n_mel_pos ||
+          text_len[i1] > text_stride || codes_len[i1] > codes_stride)
+        return fail(h, TTS_AR_ERR_CAPACITY, "text / codes length out of range");
+      const int len = text_len[i1] + 3 + codes_len[i1] + 2;
+      if (len > kMaxPagesPerSeg * kPage) return fail(h, TTS_AR_ERR_CAPACITY, "sequence longer than 1024 positions");
+      const int np = (len + kPage - 1) / kPage;
+      if (rows + len > h->rf_rows_cap || pages + np > h->n_pages || (i1 - i0) >= h->pt_rows) {
+        if (i1 == i0) return fail(h, TTS_AR_ERR_CAPACITY, "sequence exceeds re-forward row capacity");
+        break;
+      }
+      rows += len;
+      pages += np;
+      ++i1;
+    }
+    const int nb = i1 - i0;
+    std::vector<int> seq_len(nb), row_utt, row_pos, latent_dst, none;
+    for (int b = 0; b < nb; ++b) {
+      const int T = text_len[i0 + b], M = codes_len[i0 + b];
+      seq_len[b] = T + 3 + M + 2;
+      for (int p = 0; p < seq_len[b]; ++p) {
+        row_utt.push_back(b);
+        row_pos.push_back(p);
+        const int j = p - (T + 3);                          // mel position; keep j = 0 .. M-1 (:272: enc[:, -(M+2):][:, :-2])
+        latent_dst.push_back((j >= 0 && j < M) ? (i0 + b) * codes_stride + j : -1);
+      }
+    }
+    TTS_CUDA(h, cudaMemcpyAsync(h->d_text_len, text_len + i0, sizeof(int) * nb, cudaMemcpyHostToDevice, st));
+    TTS_CUDA(h, cudaMemcpyAsync(h->d_codes_len, codes_len + i0, sizeof(int) * nb, cudaMemcpyHostToDevice, st));
+    rc = run_prompt_pass(h, seq_len, row_utt, row_pos, none, latent_dst, out, false, st);
+    if (rc) return rc;
+    const int n_rows = (int)row_utt.size();
+    EmbedArgs ea{};
+    ea.x = h->d_x; ea.row_utt = h->d_pf_row_utt; ea.row_pos_in = h->d_pf_row_pos; ea.text_len = h->d_text_len;
+    ea.text = text + (size_t)i0 * text_stride; ea.text_stride = text_stride;
+    ea.codes = codes + (size_t)i0 * codes_stride; ea.codes_len = h->d_codes_len; ea.codes_stride = codes_stride;
+    ea.latent = latent + (size_t)i0 * kD;
+    ea.text_emb = h->d_text_emb; ea.text_pos = h->d_text_pos; ea.mel_emb = h->d_mel_emb; ea.mel_pos = h->d_mel_pos;
+    ea.start_text = c.start_text_token; ea.stop_text = c.stop_text_token; ea.start_mel = c.start_mel_token; ea.stop_mel = c.stop_mel_token;
+    ea.n_text_rows = c.n_text_rows; ea.n_mel_codes = c.n_mel_codes;
+    launch_embed_rows(ea, n_rows, st);
+    h->launches += 1;
+    Params P;
+    fill_common_params(h, P);
+    P.decode_mode = 0;
+    P.row_utt = h->d_pf_row_utt; P.row_pos = h->d_pf_row_pos;
+    P.mt_max = mt_max_for(n_rows);
+    P.prog = h->d_prog_pf;
+    P.n_instr = h->pf_n_instr;
+    P.n_steps = 1;
+    P.latent_out = out;
+    rc = launch(h, P, st);
+    if (rc) return rc;
+    i0 = i1;
+  }
+  TTS_CUDA(h, cudaGetLastError());
+  return 0;
+}
+
+extern "C" int tts_ar_inference_speech_host(TtsArHandle* h, const float* latent_host, const int32_t* text_host,
+                                            int32_t text_stride, const int32_t* text_len, int32_t n_utt, int32_t n_cand,
+                                            const TtsArSampling* s, int32_t max_new, int64_t* out_codes_host,
+                                            int32_t* steps_run) {
+  int rc = check_ready(h, false);
+  if (rc) return rc;
+  const TtsArConfig& c = h->cfg;
+  if (!latent_host || !text_host || !text_len || !out_codes_host || n_utt < 1 || n_cand < 1 || max_new < 1)
+    return fail(h, TTS_AR_ERR_BAD_ARG, "bad inference_speech argument");
+  if (n_utt > c.max_utts || n_utt * n_cand > c.max_seqs || text_stride > std::max(c.max_text_len, 1) || max_new > c.max_new_tokens)
+    return fail(h, TTS_AR_ERR_CAPACITY, "batch exceeds capacity");
+  cudaStream_t st = 0;   // legacy default stream of this device
+  const size_t nb_lat = sizeof(float) * (size_t)n_utt * kD, nb_txt = sizeof(int) * (size_t)n_utt * text_stride;
+  memcpy(h->h_pinned_latent, latent_host, nb_lat);
+  memcpy(h->h_pinned_text, text_host, nb_txt);
+  TTS_CUDA(h, cudaMemcpyAsync(h->d_in_latent, h->h_pinned_latent, nb_lat, cudaMemcpyHostToDevice, st));
+  TTS_CUDA(h, cudaMemcpyAsync(h->d_in_text, h->h_pinned_text, nb_txt, cudaMemcpyHostToDevice, st));
+  rc = tts_ar_prefill(h, h->d_in_latent, h->d_in_text, text_stride, text_len, n_utt, n_cand, st);
+  if (rc) return rc;
+  rc = tts_ar_generate(h, s, max_new, (int64_t*)h->d_out_codes, nullptr, nullptr, nullptr, st);
+  if (rc) return rc;
+  const size_t nb_out = sizeof(long long) * (size_t)h->n_seqs * max_new;
+  TTS_CUDA(h, cudaMemcpyAsync(h->h_pinned_codes, h->d_out_codes, nb_out, cudaMemcpyDeviceToHost, st));
+  TtsArStats stt;
+  rc = tts_ar_sync_result(h, &stt, st);
+  if (rc) return rc;
+  memcpy(out_codes_host, h->h_pinned_codes, nb_out);
+  if (steps_run) *steps_run = stt.steps_run;
+  return 0;
+}
