@@ -167,6 +167,10 @@ int tts_ar_inference_speech_host(TtsArHandle* h, const float* latent_host, const
                                  int32_t n_cand, const TtsArSampling* s, int32_t max_new,
                                  int64_t* out_codes_host, int32_t* steps_run);
 
+/* Parity hook: copies `bytes` of an internal device buffer to dst (dev).  name: "x" (residual stream, fp32
+ * [rows,1024]), "q", "logits", "cur_latent", "kv" (page pool, bf16), "ctx", "h" (bf16 fragment order). */
+int tts_ar_debug_copy(TtsArHandle* h, const char* name, void* dst, uint64_t bytes, void* stream);
+
 /* Waits for `stream`, then reports the last call's outcome. SYNC. */
 int tts_ar_sync_result(TtsArHandle* h, TtsArStats* out, void* stream);
 

@@ -1,0 +1,127 @@
+"""Staged bring-up check on the B200: localises a parity failure to a stage (embedding, LN+QKV, attention,
+MLP, head, decode step, sampler) by comparing internal buffers with the oracle.  Not part of the product.
+usage: python scripts/gpu_debug.py [stage ...]   (default: all)"""
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle.weights import ARConfig, make_state_dict, make_inputs  # noqa: E402
+from oracle.uv_oracle import OracleAR  # noqa: E402
+from tortoise_tts_b200 import UnifiedVoiceB200, ARGeometry  # noqa: E402
+
+
+def rel(a, b):
+    a, b = a.double(), b.double()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
+
+
+def stage_prefill(layers, T=12, U=1):
+    cfg = ARConfig(layers=layers)
+    sd = make_state_dict(cfg, seed=3, attn_std=0.08)
+    lat, texts = make_inputs(cfg, U, [T] * U, seed=5)
+    text = torch.stack(texts)
+    o = OracleAR(sd, cfg)
+    prefix = o.build_prefix(lat, text)
+    start = torch.full((U, 1), cfg.start_mel_token, dtype=torch.long)
+    emb = torch.cat([prefix, o.mel_emb(start, torch.arange(1))], 1)
+    x = emb
+    for i in range(layers):
+        x, _ = o._block(x, i, None)
+    logits, latv = o.head(o._ln(x, "gpt.ln_f")[:, -1])
+    m = UnifiedVoiceB200(sd, ARGeometry(layers=layers), max_utts=U, max_seqs=4 * U, max_text_len=32, max_new_tokens=16)
+    m._prefill(lat.cuda(), text.cuda(), 2)
+    st = m.sync_stats()
+    rows = U * (T + 4)
+    gx = m.debug_buffer("x", (rows, 1024)).cpu().view(U, T + 4, 1024)
+    print(f"[prefill L={layers} U={U}] watchdog={st.watchdog} x rel err {rel(gx, x):.3e}  per-row max: "
+          f"{[(float((gx[0, r] - x[0, r]).abs().max())) for r in (0, 1, T + 3)]}")
+    gl = m.logits_debug().cpu()
+    print(f"   logits rel err {rel(gl, logits):.3e}  latent rel err "
+          f"{rel(m.debug_buffer('cur_latent', (U, 1024)).cpu(), latv):.3e}")
+    m.close()
+    return rel(gl, logits)
+
+
+def stage_decode(layers=2, T=12, U=2, N=2, steps=8, **kw):
+    cfg = ARConfig(layers=layers)
+    sd = make_state_dict(cfg, seed=3, attn_std=0.08)
+    lat, texts = make_inputs(cfg, U, [T] * U, seed=5)
+    text = torch.stack(texts)
+    o = OracleAR(sd, cfg)
+    ref = o.generate(lat, text, n_cand=N, max_new=steps, want_logits=steps, **kw)
+    m = UnifiedVoiceB200(sd, ARGeometry(layers=layers), max_utts=U, max_seqs=U * N, max_text_len=32, max_new_tokens=64)
+    codes, lats, choice = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=N, max_generate_length=steps,
+                                             forced_tokens=ref["codes"], return_latents=True, return_choice=True, **kw)
+    agree = (choice.cpu().long() == ref["choice"]).float().mean().item()
+    print(f"[decode L={layers} U={U} N={N}] forced-token argmax agreement {agree:.3f}; latents rel err {rel(lats.cpu(), ref['latents']):.3e}")
+    print("   ours ", choice[0].tolist(), "\n   ref  ", ref["choice"][0].tolist())
+    # step-by-step logits with teacher forcing through tts_ar_step
+    import ctypes as C
+    m._prefill(lat.cuda(), text.cuda(), N)
+    s = m._sampling(dict(do_sample=False, **{k: v for k, v in kw.items() if k == "repetition_penalty"}))
+    errs = [rel(m.logits_debug().cpu()[:: 1], ref["logits"][0][::N])]
+    for k in range(steps - 1):
+        out = torch.zeros(U * N, 1, dtype=torch.int64, device="cuda")
+        forced = ref["codes"][:, k:k + 1].to("cuda", torch.int32).contiguous()
+        rc = m.lib.tts_ar_step(m.handle, C.byref(s), 1, C.c_void_p(out.data_ptr()), C.c_void_p(0), C.c_void_p(forced.data_ptr()),
+                               C.c_void_p(0), m._stream())
+        m._check(rc, "step")
+        m.sync_stats()
+        errs.append(rel(m.logits_debug().cpu(), ref["logits"][k + 1]))
+    print("   per-step logits rel err:", " ".join(f"{e:.2e}" for e in errs))
+    m.close()
+    return max(errs)
+
+
+def stage_full(n_cand=16, steps=64):
+    cfg = ARConfig()
+    sd = make_state_dict(cfg, seed=0)
+    lat, texts = make_inputs(cfg, 1, [64], seed=1)
+    text = torch.stack(texts)
+    g = np.load(os.path.join(ROOT, "tests", "golden", "ref_full_c1.npz"))
+    m = UnifiedVoiceB200(sd, ARGeometry(), max_utts=1, max_seqs=n_cand, max_text_len=64, max_new_tokens=520)
+    forced = torch.from_numpy(g["codes"][:, :200]).repeat(1, 1)
+    codes, choice = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=1, max_generate_length=200,
+                                       forced_tokens=forced, return_choice=True, ignore_eos=True)
+    agree = (choice.cpu().long() == torch.from_numpy(g["codes"][:, :200])).float().mean().item()
+    print(f"[full C1] teacher-forced greedy agreement with the reference over 200 steps: {agree:.4f}")
+    free = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=1, max_generate_length=200, ignore_eos=True)
+    same = (free.cpu() == torch.from_numpy(g["codes"][:, :200]))[0]
+    first_div = int((~same).nonzero()[0]) if (~same).any() else 200
+    print(f"   free-running greedy: first divergence at step {first_div}, identical {same.float().mean().item():.3f}")
+    m._prefill(lat.cuda(), text.cuda(), 1)
+    print(f"   prefill logits rel err {rel(m.logits_debug().cpu(), torch.from_numpy(g['logits_first'][0])):.3e}")
+    for nc, st in ((n_cand, steps), (n_cand, 500)):
+        t0 = time.time()
+        out = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=nc, max_generate_length=st, do_sample=True,
+                                 top_p=0.8, top_k=0, temperature=0.8, ignore_eos=True, seed=1234)
+        s = m.last_stats
+        dec_ms = s.last_device_ms - s.last_prefill_ms
+        print(f"[full N={nc} steps={st}] wall {time.time() - t0:.3f}s device {s.last_device_ms:.2f} ms (prefill {s.last_prefill_ms:.2f}) "
+              f"-> {nc * st / (s.last_device_ms * 1e-3):.0f} tok/s; decode {dec_ms / max(st - 1, 1) * 1e3:.1f} us/step; "
+              f"alg GB/s {s.last_algorithmic_bytes / (dec_ms * 1e-3) / 1e9:.0f}; uniq tokens row0 {len(set(out[0].tolist()))}")
+    m.close()
+
+
+if __name__ == "__main__":
+    which = sys.argv[1:] or ["p1", "p2", "pu", "d2", "dr", "ds", "full"]
+    torch.manual_seed(0)
+    if "p1" in which:
+        stage_prefill(1)
+    if "p2" in which:
+        stage_prefill(2)
+    if "pu" in which:
+        stage_prefill(2, T=70, U=3)
+    if "d2" in which:
+        stage_decode(2)
+    if "dr" in which:
+        stage_decode(2, repetition_penalty=2.0)
+    if "ds" in which:
+        stage_decode(2, U=1, N=20, steps=40)
+    if "full" in which:
+        stage_full()

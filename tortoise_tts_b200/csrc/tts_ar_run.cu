@@ -419,3 +419,19 @@ extern "C" int tts_ar_inference_speech_host(TtsArHandle* h, const float* latent_
   if (steps_run) *steps_run = stt.steps_run;
   return 0;
 }
+
+extern "C" int tts_ar_debug_copy(TtsArHandle* h, const char* name, void* dst, uint64_t bytes, void* stream) {
+  if (!h || !name || !dst) return TTS_AR_ERR_BAD_ARG;
+  const void* src = nullptr;
+  const std::string n(name);
+  if (n == "x") src = h->d_x;
+  else if (n == "q") src = h->d_q;
+  else if (n == "logits") src = h->d_logits;
+  else if (n == "cur_latent") src = h->d_cur_latent;
+  else if (n == "kv") src = h->d_kv;
+  else if (n == "ctx") src = h->d_ctx;
+  else if (n == "h") src = h->d_h;
+  else return fail(h, TTS_AR_ERR_BAD_ARG, "unknown debug buffer");
+  TTS_CUDA(h, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return 0;
+}
