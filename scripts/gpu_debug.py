@@ -15,6 +15,9 @@ from oracle.uv_oracle import OracleAR  # noqa: E402
 from tortoise_tts_b200 import UnifiedVoiceB200, ARGeometry  # noqa: E402
 
 
+BF16W = os.environ.get("BF16W", "1") == "1"
+
+
 def rel(a, b):
     a, b = a.double(), b.double()
     return ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
@@ -23,6 +26,7 @@ def rel(a, b):
 def stage_prefill(layers, T=12, U=1):
     cfg = ARConfig(layers=layers)
     sd = make_state_dict(cfg, seed=3, attn_std=0.08)
+    sd = {k: v.bfloat16().float() for k, v in sd.items()} if BF16W else sd
     lat, texts = make_inputs(cfg, U, [T] * U, seed=5)
     text = torch.stack(texts)
     o = OracleAR(sd, cfg)
@@ -33,7 +37,7 @@ def stage_prefill(layers, T=12, U=1):
     for i in range(layers):
         x, _ = o._block(x, i, None)
     logits, latv = o.head(o._ln(x, "gpt.ln_f")[:, -1])
-    m = UnifiedVoiceB200(sd, ARGeometry(layers=layers), max_utts=U, max_seqs=4 * U, max_text_len=32, max_new_tokens=16)
+    m = UnifiedVoiceB200(sd, ARGeometry(layers=layers), max_utts=U, max_seqs=4 * U, max_text_len=max(32, T), max_new_tokens=16)
     m._prefill(lat.cuda(), text.cuda(), 2)
     st = m.sync_stats()
     rows = U * (T + 4)
@@ -50,6 +54,7 @@ def stage_prefill(layers, T=12, U=1):
 def stage_decode(layers=2, T=12, U=2, N=2, steps=8, **kw):
     cfg = ARConfig(layers=layers)
     sd = make_state_dict(cfg, seed=3, attn_std=0.08)
+    sd = {k: v.bfloat16().float() for k, v in sd.items()} if BF16W else sd
     lat, texts = make_inputs(cfg, U, [T] * U, seed=5)
     text = torch.stack(texts)
     o = OracleAR(sd, cfg)

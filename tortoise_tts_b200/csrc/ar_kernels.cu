@@ -11,7 +11,7 @@ namespace tts {
 // Warps 0..15: consumers (compute, grid barriers).  Warp 16: producer (weight stream).  The producer is not
 // gated by the grid barriers -- weights do not depend on activations -- so HBM keeps streaming the next
 // stage's (and next layer's, next step's) weights while the consumers wait on a barrier or do attention.
-__global__ void __maxnreg__(120) ar_program_kernel(const __grid_constant__ Params P) {
+__global__ void __launch_bounds__(kThreads, 1) ar_program_kernel(const __grid_constant__ Params P) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const Smem sm = carve_smem(smem_raw, P.mt_max);
   Ctrl* c = sm.ctrl;
