@@ -113,6 +113,8 @@ typedef struct {
   double last_algorithmic_bytes;/* SURVEY.md 8(d) bytes of the last generate/step call */
   float last_device_ms;         /* CUDA-event time of the last prefill+generate on its stream */
   float last_prefill_ms;
+  int32_t kv_pages;             /* pages in the KV pool (32 positions x 16 heads x K,V per layer each) */
+  int32_t ctas;                 /* CTAs of the persistent kernel (== SMs) */
 } TtsArStats;
 
 int tts_ar_abi_version(void);

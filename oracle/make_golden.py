@@ -48,25 +48,30 @@ def case_l2():
     print("ref_l2 done", r["codes"][0].tolist())
 
 
-def case_full():
+def case_full(bf16_weights=False):
     """BASELINE config C1: 30 layers fp32, one utterance T=64, 1 candidate, greedy, 200 tokens,
-    stop token ignored so exactly 200 steps run."""
+    stop token ignored so exactly 200 steps run.  bf16_weights=True: the same run with every weight
+    rounded to a bf16-representable value first (still fp32 arithmetic in the reference), i.e. the
+    reference and the bf16 CUDA path hold IDENTICAL weights -> ref_full_c1_bf16w.npz."""
     cfg = ARConfig()
     spec = dict(layers=30, w_seed=0, w_std=0.02, in_seed=1, n_utt=1, text_len=64, n_cand=1, max_new=200,
-                ignore_eos=True)
+                ignore_eos=True, bf16_weights=bf16_weights)
     sd = make_state_dict(cfg, seed=0)
+    if bf16_weights:
+        sd = {k: v.bfloat16().float() for k, v in sd.items()}
     lat, texts = make_inputs(cfg, 1, [64], seed=1)
     text = torch.stack(texts)
     m = ref_shim.build_reference_model(sd, cfg)
     r = ref_shim.ref_generate(m, lat, text, n_cand=1, max_new=200, want_logits=200, ignore_eos=True)
     lg = r["logits"]                                   # [200, 1, V]
     top2 = torch.topk(lg[:, 0], 2, dim=-1)
-    np.savez_compressed(os.path.join(OUT, "ref_full_c1.npz"), spec=str(spec), versions=str(versions()),
+    name = "ref_full_c1_bf16w.npz" if bf16_weights else "ref_full_c1.npz"
+    np.savez_compressed(os.path.join(OUT, name), spec=str(spec), versions=str(versions()),
                         codes=r["codes"].numpy(), logits_first=lg[:2].numpy(), logits_last=lg[-1:].numpy(),
                         top2_vals=top2.values.numpy(), top2_idx=top2.indices.numpy(),
                         latents_sel=r["latents"][:, [0, 1, 199]].numpy(),
                         pos_trace=np.array(r["pos_trace"]), prefix_len=r["prefix_len"])
-    print("ref_full_c1 done", r["codes"][0, :12].tolist())
+    print(name, "done", r["codes"][0, :12].tolist())
 
 
 def case_warpers():
@@ -98,3 +103,4 @@ if __name__ == "__main__":
     case_warpers()
     case_l2()
     case_full()
+    case_full(bf16_weights=True)

@@ -1,0 +1,371 @@
+"""GPU (-m gpu): the CUDA path, called through the C ABI (ctypes, tortoise_tts_b200/_lib.py), against
+ (a) golden vectors produced by the REFERENCE's own classes (tests/golden/*.npz, oracle/make_golden.py) and
+ (b) the CPU oracle (oracle/uv_oracle.py, pinned to (a) by tests/test_oracle_golden.py) on the same seeded
+     inputs.
+Tolerances (BASELINE.json north_star): logits within 2e-2 relative (max |diff| / max |ref|) in bf16;
+KV-cache indexing, stop-token handling and every integer output bit-exact.
+"""
+import ast
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import philox
+from oracle.uv_oracle import (OracleAR, apply_repetition_penalty, apply_temperature, apply_top_k, apply_top_p)
+from oracle.weights import ARConfig, make_inputs, make_state_dict
+
+pytestmark = pytest.mark.gpu
+
+BF16_REL = 2e-2          # north_star: "prefill and step logits within 2e-2 relative error in bf16"
+STRESS_REL = 4e-2        # sharpened-attention stress weights (attn_std 0.08): torch's own bf16 path is at 2.4e-2
+
+
+def rel(a, b):
+    a, b = torch.as_tensor(a).double().cpu(), torch.as_tensor(b).double().cpu()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
+
+
+@pytest.fixture(scope="module")
+def b200():
+    import __graft_entry__ as g
+    g.build()
+    from tortoise_tts_b200 import ARGeometry, UnifiedVoiceB200
+    return UnifiedVoiceB200, ARGeometry
+
+
+def bf16_weights(sd):
+    """bf16-representable weights: the fp32 oracle and the bf16 CUDA path then hold IDENTICAL weights."""
+    return {k: v.bfloat16().float() for k, v in sd.items()}
+
+
+@pytest.fixture(scope="module")
+def l2_case(golden_dir):
+    g = np.load(os.path.join(golden_dir, "ref_l2.npz"))
+    spec = ast.literal_eval(str(g["spec"]))
+    cfg = ARConfig(layers=spec["layers"])
+    sd = make_state_dict(cfg, seed=spec["w_seed"], attn_std=spec["attn_std"])
+    lat, texts = make_inputs(cfg, spec["n_utt"], [spec["text_len"]] * spec["n_utt"], seed=spec["in_seed"])
+    return g, spec, cfg, sd, lat, torch.stack(texts)
+
+
+# ---- against the reference's golden vectors ------------------------------------------------------------
+def test_l2_reference_golden_teacher_forced(b200, l2_case):
+    """2 layers, sharpened attention, 2 utterances x 2 candidates, repetition_penalty 2.0: prefill and
+    step logits, per-step latents, greedy choices under teacher forcing with the reference's codes."""
+    UV, Geo = b200
+    g, spec, cfg, sd, lat, text = l2_case
+    m = UV(sd, Geo(layers=2), max_utts=2, max_seqs=4, max_text_len=16, max_new_tokens=16)
+    ref_codes = torch.from_numpy(g["codes"])
+    codes, lats, choice = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=2, max_generate_length=10,
+                                             repetition_penalty=2.0, forced_tokens=ref_codes, return_latents=True,
+                                             return_choice=True)
+    assert torch.equal(codes.cpu(), ref_codes)                       # forced ids are written back bit-exact
+    assert rel(lats, g["latents"]) < STRESS_REL
+    agree = (choice.cpu().long() == ref_codes).float().mean().item()
+    assert agree >= 0.9, agree
+    # step logits through the streaming entry (tts_ar_step), still teacher-forced
+    m._prefill(lat.cuda(), text.cuda(), 2)
+    s = m._sampling(dict(do_sample=False, repetition_penalty=2.0))
+    errs = [rel(m.logits_debug(), g["logits"][0][::2])]               # prefill: one row per utterance
+    for k in range(2):
+        out = torch.zeros(4, 1, dtype=torch.int64, device="cuda")
+        forced = ref_codes[:, k:k + 1].to("cuda", torch.int32).contiguous()
+        m._check(m.lib.tts_ar_step(m.handle, C.byref(s), 1, C.c_void_p(out.data_ptr()), C.c_void_p(0),
+                                   C.c_void_p(forced.data_ptr()), C.c_void_p(0), m._stream()), "step")
+        m.sync_stats()
+        errs.append(rel(m.logits_debug(), g["logits"][k + 1]))
+    assert max(errs) < STRESS_REL, errs
+    m.close()
+
+
+def test_l2_reference_golden_latent_reforward(b200, l2_case):
+    """UnifiedVoice.forward(return_latent=True) (unified_voice.py:544-600) vs the reference's output."""
+    UV, Geo = b200
+    g, spec, cfg, sd, lat, text = l2_case
+    m = UV(sd, Geo(layers=2), max_utts=2, max_seqs=4, max_text_len=16, max_new_tokens=16)
+    codes = torch.from_numpy(g["reforward_codes"])
+    B, M = codes.shape
+    l2, t2 = lat.repeat_interleave(2, 0), text.repeat_interleave(2, 0)
+    out = m.forward(l2.cuda(), t2.cuda(), torch.full((B,), t2.shape[1]), codes.cuda(), torch.full((B,), M * 1024),
+                    return_latent=True, clip_inputs=False)
+    assert out.shape == (B, M, 1024)
+    assert rel(out, g["reforward_latents"]) < STRESS_REL
+    m.close()
+
+
+@pytest.fixture(scope="module")
+def full_model(b200):
+    UV, Geo = b200
+    cfg = ARConfig()
+    sd = bf16_weights(make_state_dict(cfg, seed=0))
+    lat, texts = make_inputs(cfg, 1, [64], seed=1)
+    m = UV(sd, Geo(), max_utts=1, max_seqs=16, max_text_len=64, max_new_tokens=520)
+    yield m, cfg, lat, torch.stack(texts)
+    m.close()
+
+
+def test_full_c1_reference_golden(full_model, golden_dir):
+    """BASELINE config C1 (30 layers, T=64, 1 candidate, greedy, 200 tokens) on IDENTICAL (bf16-representable)
+    weights: prefill logits within 2e-2; greedy choices under teacher forcing vs the reference's 200 tokens.
+    With random-init weights 20% of the reference's own top-2 gaps are below 1e-2 of the logit scale, so the
+    argmax criterion is applied where the reference's gap exceeds the logits tolerance actually achieved."""
+    m, cfg, lat, text = full_model
+    g = np.load(os.path.join(golden_dir, "ref_full_c1_bf16w.npz"))
+    ref = torch.from_numpy(g["codes"][:, :200])
+    m._prefill(lat.cuda(), text.cuda(), 1)
+    e0 = rel(m.logits_debug(), g["logits_first"][0])
+    assert e0 < BF16_REL, e0
+    codes, choice, lats = None, None, None
+    codes, lats, choice = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=1, max_generate_length=200,
+                                             forced_tokens=ref, return_latents=True, return_choice=True, ignore_eos=True)
+    assert torch.equal(codes.cpu(), ref)
+    same = (choice.cpu().long() == ref)[0].numpy()
+    gap = g["top2_vals"][:, 0] - g["top2_vals"][:, 1]
+    scale = float(np.abs(g["logits_first"]).max())
+    clear = gap > 2 * e0 * scale                      # the reference's own decision is outside our error band
+    print(f"C1 teacher-forced agreement {same.mean():.4f} overall, {same[clear].mean():.4f} on {clear.sum()} clear steps; "
+          f"prefill logits rel err {e0:.2e}")
+    assert same[clear].mean() >= 0.99
+    assert same.mean() >= 0.95
+    assert rel(lats[:, [0, 1, 199]], g["latents_sel"]) < BF16_REL
+
+
+def test_full_c1_original_fp32_weights(b200, golden_dir):
+    """Same, with the reference holding unrounded fp32 weights (ref_full_c1.npz): the bf16 snapshot of the weights
+    is now part of the error."""
+    UV, Geo = b200
+    cfg = ARConfig()
+    sd = make_state_dict(cfg, seed=0)
+    lat, texts = make_inputs(cfg, 1, [64], seed=1)
+    text = torch.stack(texts)
+    g = np.load(os.path.join(golden_dir, "ref_full_c1.npz"))
+    m = UV(sd, Geo(), max_utts=1, max_seqs=1, max_text_len=64, max_new_tokens=8)
+    m._prefill(lat.cuda(), text.cuda(), 1)
+    assert rel(m.logits_debug(), g["logits_first"][0]) < BF16_REL
+    m.close()
+
+
+# ---- against the oracle on the same seeded inputs -------------------------------------------------------------
+def make_small(b200, layers=2, U=2, T=12, attn_std=0.04, **kw):
+    UV, Geo = b200
+    cfg = ARConfig(layers=layers)
+    sd = bf16_weights(make_state_dict(cfg, seed=7, attn_std=attn_std))
+    lens = T if isinstance(T, (list, tuple)) else [T] * U
+    lat, texts = make_inputs(cfg, U, lens, seed=9)
+    m = UV(sd, Geo(layers=layers), max_text_len=max(max(lens), 8), **kw)
+    return m, OracleAR(sd, cfg), cfg, lat, texts
+
+
+def kv_rows(m, layer, page, kv, head, n_pages):
+    """Python restatement of layout.h kv_row_offset: pool[layer][page][kv][head][slot 32][64] bf16."""
+    pool = m.debug_buffer("kv", ((layer + 1) * n_pages * 2 * 16 * 32 * 64,), dtype=torch.bfloat16)
+    off = ((((layer * n_pages + page) * 2 + kv) * 16 + head) * 32) * 64
+    return pool[off: off + 32 * 64].view(32, 64).float().cpu()
+
+
+def test_kv_cache_indexing_and_prefix_sharing(b200):
+    """Prompt K rows land in the utterance's shared prefix pages at slot = position % 32; decode K rows of
+    candidate c land in ITS private pages; candidates of one utterance share the prompt pages (values vs the
+    oracle's DynamicCache-equivalent past, bf16 tolerance; the mapping itself is exact or the values are garbage)."""
+    T = 40                                               # P+1 = 44 -> 2 prefix pages per utterance
+    m, o, cfg, lat, texts = make_small(b200, U=2, T=T, max_utts=2, max_seqs=6, max_new_tokens=40)
+    text = torch.stack(texts)
+    N, steps = 3, 36                                     # private segment crosses a page boundary (32)
+    ref = o.generate(lat, text, n_cand=N, max_new=steps, ignore_eos=True)
+    m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=N, max_generate_length=steps,
+                       forced_tokens=ref["codes"], ignore_eos=True)
+    # oracle cache for sequence (u=1, c=2): replay to get K of layer 1
+    logits, _, past, P = o.prefill(lat, text, N)
+    for k in range(steps - 1):
+        logits, _, past = o.step(ref["codes"][:, k], k + 1, past)
+    K = past[1][0]                                       # layer 1 keys [B, H, L, 64]
+    V = past[1][1]
+    nqp = (m.cfg.max_new_tokens + 31) // 32              # private pages reserved per sequence by create()
+    n_pages = m.last_stats.kv_pages
+    plen = T + 4
+    pp = (plen + 31) // 32                               # prefix pages actually used per utterance
+    seq, head = 1 * N + 2, 5
+    # prompt page 1 of utterance 1 = global page pp*1 + 1
+    got = kv_rows(m, 1, pp * 1 + 1, 0, head, n_pages)[: plen - 32]
+    assert rel(got, K[seq, head, 32:plen]) < 1e-2
+    got = kv_rows(m, 1, pp * 1 + 0, 1, head, n_pages)
+    assert rel(got, V[seq, head, :32]) < 1e-2
+    # private pages start after all prompt pages: sequence s owns [2*pp + s*nqp, ...)
+    base = 2 * pp + seq * nqp
+    got = kv_rows(m, 1, base, 0, head, n_pages)
+    assert rel(got, K[seq, head, plen:plen + 32]) < 1e-2
+    got = kv_rows(m, 1, base + 1, 0, head, n_pages)[: steps - 1 - 32]
+    assert rel(got, K[seq, head, plen + 32: plen + steps - 1]) < 1e-2
+    m.close()
+
+
+def test_stop_token_handling_bit_exact(b200):
+    """Quirk Q7 (stream_generator.py:1169-1190): a row that emits 8193 keeps emitting 8193, the other rows go
+    on, the loop ends when every row has finished (rectangular output, early exit) or at max_new."""
+    m, o, cfg, lat, texts = make_small(b200, U=2, T=10, max_utts=2, max_seqs=4, max_new_tokens=32)
+    text = torch.stack(texts)
+    stop = cfg.stop_mel_token
+    forced = torch.randint(0, 8192, (4, 20), generator=torch.Generator().manual_seed(3))
+    forced[0, 3] = stop
+    forced[1, 0] = stop
+    forced[2, 11] = stop
+    forced[3, 7] = stop
+    ref = o.generate(lat, text, n_cand=2, max_new=20, forced=forced)
+    got, choice = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=2, max_generate_length=20,
+                                     forced_tokens=forced, return_choice=True)
+    assert got.shape == ref["codes"].shape == (4, 12)                 # stopped after the last row finished
+    assert torch.equal(got.cpu(), ref["codes"])
+    assert m.last_stats.all_finished == 1
+    for r, k in ((0, 3), (1, 0), (2, 11), (3, 7)):
+        assert (got[r, k:] == stop).all()
+    # no stop: runs to max_new exactly; ignore_eos: a forced stop does not finish the row
+    got2 = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=2, max_generate_length=7,
+                              forced_tokens=forced[:, 4:11].contiguous())
+    assert got2.shape == (4, 7) and m.last_stats.all_finished == 0
+    got3 = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=2, max_generate_length=20,
+                              forced_tokens=forced, ignore_eos=True)
+    assert got3.shape == (4, 20) and torch.equal(got3.cpu(), forced)
+    m.close()
+
+
+def test_greedy_free_running_matches_oracle(b200):
+    """Free-running greedy with repetition_penalty 2.0 (train.py:127) on a model with clear decisions
+    (sharper head): token sequences identical to the oracle's."""
+    UV, Geo = b200
+    cfg = ARConfig(layers=2)
+    sd = make_state_dict(cfg, seed=7, attn_std=0.04)
+    sd["mel_head.weight"] = sd["mel_head.weight"] * 8.0
+    sd = bf16_weights(sd)
+    lat, texts = make_inputs(cfg, 2, [12, 12], seed=9)
+    text = torch.stack(texts)
+    o = OracleAR(sd, cfg)
+    ref = o.generate(lat, text, n_cand=2, max_new=48, repetition_penalty=2.0, want_logits=48)
+    m = UV(sd, Geo(layers=2), max_utts=2, max_seqs=4, max_text_len=16, max_new_tokens=64)
+    got = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=2, max_generate_length=48,
+                             repetition_penalty=2.0)
+    same = (got.cpu() == ref["codes"]).float().mean().item()
+    print("free-running greedy identical fraction", same)
+    assert same >= 0.99
+    m.close()
+
+
+def test_ragged_batch_equals_single_utterance_runs(b200):
+    """Quirk Q8 contract: a ragged batch (each utterance at its true text length, paged KV) gives, per
+    utterance, what the oracle gives for that utterance alone."""
+    lens = [5, 33, 18]
+    m, o, cfg, lat, texts = make_small(b200, U=3, T=lens, max_utts=3, max_seqs=6, max_new_tokens=16)
+    Tm = max(lens)
+    text = torch.zeros(3, Tm, dtype=torch.long)
+    for u, t in enumerate(texts):
+        text[u, : len(t)] = t
+    forced = torch.randint(0, 8192, (6, 6), generator=torch.Generator().manual_seed(5))
+    got, lats = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=2, max_generate_length=6,
+                                   text_lengths=lens, forced_tokens=forced, return_latents=True)
+    for u in range(3):
+        ref = o.generate(lat[u:u + 1], texts[u][None], n_cand=2, max_new=6, forced=forced[2 * u: 2 * u + 2])
+        assert rel(lats[2 * u: 2 * u + 2], ref["latents"]) < BF16_REL, u
+    m.close()
+
+
+@pytest.mark.parametrize("kw", [dict(top_p=0.8, temperature=0.8, top_k=0), dict(top_k=16, temperature=1.3, top_p=1.0),
+                                dict(top_k=50, top_p=0.5, temperature=0.7, repetition_penalty=2.0)])
+def test_device_sampler_equals_oracle_on_device_logits(b200, kw):
+    """The fused warpers + Philox inverse-CDF multinomial vs the oracle's HF-equivalent processors
+    (pinned to HF's own classes by tests/test_oracle_golden.py) applied to the DEVICE's logits: identical
+    tokens except where u*Z is within fp32 summation-order distance of a CDF edge."""
+    m, o, cfg, lat, texts = make_small(b200, U=1, T=12, max_utts=1, max_seqs=24, max_new_tokens=16)
+    text = torch.stack(texts)
+    N, seed, base = 24, 4321, 1000
+    m._prefill(lat.cuda(), text.cuda(), N)
+    s = m._sampling(dict(do_sample=True, seed=seed, seq_index_base=base, **kw))
+    ids = torch.full((N, text.shape[1] + 4), 1, dtype=torch.long)
+    ids[:, -1] = cfg.start_mel_token
+    n_checked = 0
+    for step in range(6):
+        lg = m.logits_debug().cpu()
+        if step == 0:
+            lg = lg.repeat_interleave(N, 0)
+        sc = apply_repetition_penalty(lg.clone(), ids, kw.get("repetition_penalty", 1.0))
+        sc = apply_top_p(apply_top_k(apply_temperature(sc, kw["temperature"]), kw["top_k"]), kw["top_p"])
+        out = torch.zeros(N, 1, dtype=torch.int64, device="cuda")
+        m._check(m.lib.tts_ar_step(m.handle, C.byref(s), 1, C.c_void_p(out.data_ptr()), C.c_void_p(0), C.c_void_p(0),
+                                   C.c_void_p(0), m._stream()), "step")
+        m.sync_stats()
+        out = out.cpu()[:, 0]
+        for r in range(N):
+            tok, margin = philox.multinomial_row(sc[r].numpy(), philox.uniform(seed, base + r, step))
+            assert torch.isfinite(sc[r, out[r]]), "device sampled a token outside the HF support set"
+            if margin > 1e-5:
+                assert int(out[r]) == tok, (step, r, int(out[r]), tok, margin)
+                n_checked += 1
+        ids = torch.cat([ids, out[:, None]], 1)
+    assert n_checked > 0.9 * 6 * N
+    m.close()
+
+
+def test_sampling_is_invariant_to_sharding(b200):
+    """Philox key = (seed, GLOBAL sequence index, step): 8 candidates in one call == two calls of 4 with
+    seq_index_base 0 and 4 (what two ranks would run)."""
+    m, o, cfg, lat, texts = make_small(b200, U=1, T=12, max_utts=1, max_seqs=8, max_new_tokens=16)
+    text = torch.stack(texts)
+    kw = dict(do_sample=True, top_p=0.8, temperature=0.8, top_k=0, seed=77, max_generate_length=12, ignore_eos=True)
+    whole = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=8, **kw).cpu()
+    a = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=4, seq_index_base=0, **kw).cpu()
+    b = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=4, seq_index_base=4, **kw).cpu()
+    assert torch.equal(whole, torch.cat([a, b]))
+    again = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=8, **kw).cpu()
+    assert torch.equal(whole, again)                    # deterministic
+    m.close()
+
+
+def test_streaming_generator_matches_batch_path(b200):
+    m, o, cfg, lat, texts = make_small(b200, U=1, T=12, max_utts=1, max_seqs=2, max_new_tokens=40)
+    text = torch.stack(texts)
+    ids = m.compute_embeddings(lat.cuda(), text.cuda())
+    assert ids.shape == (1, 16) and int(ids[0, -1]) == cfg.start_mel_token and (ids[0, :-1] == 1).all()
+    kw = dict(do_sample=True, top_p=0.8, temperature=0.8, top_k=0, seed=5)
+    toks, lts = [], []
+    for t, l in m.get_generator(ids, max_length=16 + 20, num_return_sequences=2, chunk=8, **kw):   # Q9: total length
+        toks.append(t.cpu())
+        lts.append(l.cpu())
+    toks = torch.stack(toks, 1)
+    assert toks.shape == (2, 20)
+    whole, lats = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=2, max_generate_length=20,
+                                     return_latents=True, **kw)
+    assert torch.equal(toks, whole.cpu())
+    assert torch.equal(torch.stack(lts, 1), lats.cpu())
+    m.close()
+
+
+def test_host_buffer_entry_and_errors(b200):
+    m, o, cfg, lat, texts = make_small(b200, U=1, T=12, max_utts=1, max_seqs=4, max_new_tokens=16)
+    text = torch.stack(texts)
+    kw = dict(do_sample=True, top_p=0.8, temperature=0.8, top_k=0, seed=5, ignore_eos=True)
+    a = m.inference_speech_host(lat, text, num_return_sequences=4, max_generate_length=10, **kw)
+    b = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=4, max_generate_length=10, **kw)
+    assert a.device.type == "cpu" and torch.equal(a, b.cpu())
+    with pytest.raises(ValueError):
+        m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=5, max_generate_length=4)    # capacity
+    with pytest.raises(ValueError):
+        m.inference_speech(lat.cuda(), text.cuda(), do_sample=True, temperature=0.0)
+    with pytest.raises(NotImplementedError):
+        m.inference_speech(lat.cuda(), text.cuda(), num_beams=4)
+    m.close()
+
+
+def test_c2_shape_properties(full_model):
+    """BASELINE config C2 at full size (16 candidates, top-p 0.8, 500 tokens): size-independent properties --
+    determinism, candidates differ, every sampled id is a valid mel code, a sequence prefix does not depend on how
+    many steps are requested, and the watchdog never fires."""
+    m, cfg, lat, text = full_model
+    kw = dict(do_sample=True, top_p=0.8, temperature=0.8, top_k=0, seed=1234, ignore_eos=True)
+    a = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=16, max_generate_length=500, **kw).cpu()
+    st = m.last_stats
+    assert a.shape == (16, 500) and st.watchdog == 0 and st.steps_run == 500
+    assert int(a.min()) >= 0 and int(a.max()) < cfg.number_mel_codes
+    assert len({tuple(r.tolist()) for r in a}) == 16
+    b = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=16, max_generate_length=120, **kw).cpu()
+    assert torch.equal(a[:, :120], b)

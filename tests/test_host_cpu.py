@@ -1,0 +1,174 @@
+"""CPU: the C-ABI library loads and exports what include/tts_ar.h declares, the layout arithmetic is
+consistent, and the host-side sharding logic (world_size 2, gloo) reassembles the global code matrix."""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def built():
+    sys.path.insert(0, ROOT)
+    import __graft_entry__ as g
+    g.build()
+    return g
+
+
+def test_c_abi_exports_every_declared_symbol(built):
+    hdr = open(os.path.join(ROOT, "include", "tts_ar.h")).read()
+    declared = set(re.findall(r"\b(tts_ar_[a-z_0-9]+)\s*\(", hdr))
+    assert len(declared) >= 13
+    lib = C.CDLL(os.path.join(ROOT, "tortoise_tts_b200", "lib", "libtts_ar.so"))
+    for name in declared:
+        assert hasattr(lib, name), name
+    lib.tts_ar_abi_version.restype = C.c_int
+    assert lib.tts_ar_abi_version() == 1
+    from tortoise_tts_b200 import _lib
+    assert set(_lib.SYMBOLS) == declared
+
+
+def test_product_fails_loudly_without_a_gpu(built):
+    """No CPU fallback: creating a handle on a box without an sm_100 device must raise."""
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from tortoise_tts_b200 import UnifiedVoiceB200
+    with pytest.raises(RuntimeError):
+        UnifiedVoiceB200({}, device="cpu")
+    with pytest.raises(RuntimeError):
+        UnifiedVoiceB200({}, device="cuda:0")
+
+
+def test_product_does_not_import_the_oracle():
+    pkg = os.path.join(ROOT, "tortoise_tts_b200")
+    for dp, _, fs in os.walk(pkg):
+        for f in fs:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dp, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle", src, re.M), f
+
+
+@pytest.fixture(scope="module")
+def lc(built):
+    lib = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "liblayout_check.so"))
+    lib.lc_afrag_elem_offset.restype = C.c_longlong
+    lib.lc_kv_row_offset.restype = C.c_longlong
+    lib.lc_float_key.restype = C.c_uint
+    lib.lc_float_key.argtypes = [C.c_uint]
+    return lib
+
+
+def test_weight_chunk_map_is_a_bijection(lc):
+    seen = np.zeros(1024 * 8, dtype=np.int32)
+    for k in range(1024):
+        for n in range(8):
+            seen[lc.lc_chunk_elem_offset(k, n)] += 1
+    assert (seen == 1).all()
+    assert lc.lc_chunk_bytes() == 16384
+    # the two k of a 32-bit word are adjacent; the four words of a lane's uint4 are b0/b1 of two k16-blocks
+    assert lc.lc_chunk_elem_offset(1, 0) == lc.lc_chunk_elem_offset(0, 0) + 1
+    assert lc.lc_chunk_elem_offset(8, 0) == lc.lc_chunk_elem_offset(0, 0) + 2
+    assert lc.lc_chunk_elem_offset(16, 0) == lc.lc_chunk_elem_offset(0, 0) + 4
+
+
+def test_afrag_map_is_a_bijection(lc):
+    for K in (1024, 4096):
+        offs = {lc.lc_afrag_elem_offset(r, c, K) for r in range(32) for c in range(0, K, 1)}
+        assert len(offs) == 32 * K and max(offs) == 32 * K - 1
+
+
+def test_kv_page_rows_do_not_overlap(lc):
+    n_pages = 5
+    offs = set()
+    for layer in range(2):
+        for page in range(n_pages):
+            for kv in range(2):
+                for head in range(16):
+                    for slot in range(32):
+                        offs.add(lc.lc_kv_row_offset(layer, n_pages, page, kv, head, slot))
+    assert len(offs) == 2 * n_pages * 2 * 16 * 32
+    assert all(o % 64 == 0 for o in offs) and max(offs) == (len(offs) - 1) * 64
+
+
+@pytest.mark.parametrize("G", [148, 132, 7])
+def test_tile_schedule_covers_every_tile_once(lc, G):
+    rot = 0
+    for n_tiles in (384, 128, 512, 128, 1025):
+        got = []
+        t0, cnt = C.c_int(), C.c_int()
+        for cta in range(G):
+            lc.lc_tile_range(n_tiles, G, rot, cta, C.byref(t0), C.byref(cnt))
+            got += list(range(t0.value, t0.value + cnt.value))
+        assert sorted(got) == list(range(n_tiles))
+        rot = lc.lc_next_rot(n_tiles, G, rot)
+        assert 0 <= rot < G
+
+
+def test_float_key_is_monotone(lc):
+    vals = np.array([-np.inf, -3.5, -1e-30, -0.0, 0.0, 1e-30, 2.0, 7.25, np.inf], dtype=np.float32)
+    keys = [lc.lc_float_key(int(v.view(np.uint32))) for v in vals]
+    assert all(a <= b for a, b in zip(keys, keys[1:]))
+    assert keys[0] < keys[1] and keys[-2] < keys[-1]
+
+
+def test_plan_shards():
+    from tortoise_tts_b200.shard import plan_shards
+    s = plan_shards(1, 256, 8)                       # C3: one utterance, 256 candidates, 8 GPUs
+    assert [x.n_seqs for x in s] == [32] * 8 and [x.seq_index_base for x in s] == list(range(0, 256, 32))
+    s = plan_shards(64, 16, 8)                       # C4: utterance-major
+    assert [x.n_utt for x in s] == [8] * 8 and s[3].seq_index_base == 24 * 16
+    s = plan_shards(3, 5, 2)
+    assert sorted(i for x in s for i in x.global_indices()) == list(range(15))
+    s = plan_shards(2, 6, 8)
+    assert sorted(i for x in s for i in x.global_indices()) == list(range(12))
+    s = plan_shards(3, 4, 8)                         # 2 ranks per utterance, 2 idle
+    assert sorted(i for x in s for i in x.global_indices()) == list(range(12))
+
+
+_WORKER = r'''
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+from tortoise_tts_b200.shard import plan_shards, gather_codes
+dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%s" % sys.argv[2], rank=int(sys.argv[3]), world_size=2)
+rank = dist.get_rank()
+for (U, N) in ((1, 6), (3, 2)):
+    shards = plan_shards(U, N, 2)
+    me = shards[rank]
+    steps = 4 + rank                                  # ranks stop at different lengths
+    g = torch.tensor(me.global_indices())
+    codes = (g[:, None] * 100 + torch.arange(steps)[None]).long()
+    lat = codes[..., None].float().repeat(1, 1, 3)
+    out, out_lat = gather_codes(codes, 8193, shards, latents=lat)
+    assert out.shape == (U * N, 5), out.shape
+    for i in range(U * N):
+        r = [k for k, s in enumerate(shards) if i in s.global_indices()][0]
+        n = 4 + r
+        assert out[i, :n].tolist() == [i * 100 + k for k in range(n)], (i, out[i])
+        assert (out[i, n:] == 8193).all()
+        assert out_lat[i, :n, 0].tolist() == [float(i * 100 + k) for k in range(n)]
+dist.barrier()
+dist.destroy_process_group()
+print("ok", rank)
+'''
+
+
+def test_gather_codes_world2_gloo(tmp_path):
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    script = tmp_path / "w.py"
+    script.write_text(_WORKER)
+    procs = [subprocess.Popen([sys.executable, str(script), ROOT, str(port), str(r)], stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT, text=True) for r in range(2)]
+    outs = [p.communicate(timeout=240)[0] for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o
+        assert "ok" in o

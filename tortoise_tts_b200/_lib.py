@@ -48,7 +48,8 @@ class TtsArSampling(C.Structure):
 class TtsArStats(C.Structure):
     _fields_ = [("struct_size", C.c_int32), ("steps_run", C.c_int32), ("all_finished", C.c_int32),
                 ("watchdog", C.c_int32), ("kernel_launches", C.c_int64), ("last_algorithmic_bytes", C.c_double),
-                ("last_device_ms", C.c_float), ("last_prefill_ms", C.c_float)]
+                ("last_device_ms", C.c_float), ("last_prefill_ms", C.c_float),
+                ("kv_pages", C.c_int32), ("ctas", C.c_int32)]
 
 
 _lib = None

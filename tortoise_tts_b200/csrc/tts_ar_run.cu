@@ -307,6 +307,8 @@ extern "C" int tts_ar_sync_result(TtsArHandle* h, TtsArStats* out, void* stream)
   out->all_finished = h->h_pinned_i[2] == 0;
   out->kernel_launches = h->launches;
   out->last_algorithmic_bytes = h->last_bytes;
+  out->kv_pages = h->n_pages;
+  out->ctas = h->G;
   if (h->timing_valid) {
     float a = 0.f, b = 0.f;
     if (cudaEventElapsedTime(&a, h->ev0, h->ev1) == cudaSuccess) out->last_prefill_ms = a;
