@@ -32,7 +32,7 @@ if ROOT not in sys.path:
 
 N_CAND = 16
 TEXT_LEN = 64
-MAX_NEW = 500
+MAX_NEW = int(os.environ.get("TTS_BENCH_MAX_NEW", "500"))   # override ONLY for short ncu captures (not a bench value)
 SAMPLING = dict(do_sample=True, top_p=0.8, temperature=0.8, top_k=0, repetition_penalty=1.0, seed=1234)
 REF_SAMPLE_TOKENS = 24          # --impl reference: decode steps per timed step (bounded sample)
 METRIC = "AR mel tokens/sec"

@@ -232,8 +232,9 @@ def test_stop_token_handling_bit_exact(b200):
 
 
 def test_greedy_free_running_matches_oracle(b200):
-    """Free-running greedy with repetition_penalty 2.0 (train.py:127) on a model with clear decisions
-    (sharper head): token sequences identical to the oracle's."""
+    """Free-running greedy with repetition_penalty 2.0 (train.py:127): every row is identical to the oracle's up to
+    its first divergence, and a divergence may only happen where the oracle's own top-2 gap is inside the bf16
+    logits tolerance (a tie the reference itself would break differently in bf16)."""
     UV, Geo = b200
     cfg = ARConfig(layers=2)
     sd = make_state_dict(cfg, seed=7, attn_std=0.04)
@@ -242,13 +243,27 @@ def test_greedy_free_running_matches_oracle(b200):
     lat, texts = make_inputs(cfg, 2, [12, 12], seed=9)
     text = torch.stack(texts)
     o = OracleAR(sd, cfg)
-    ref = o.generate(lat, text, n_cand=2, max_new=48, repetition_penalty=2.0, want_logits=48)
+    steps = 48
+    ref = o.generate(lat, text, n_cand=2, max_new=steps, repetition_penalty=2.0, want_logits=steps)
     m = UV(sd, Geo(layers=2), max_utts=2, max_seqs=4, max_text_len=16, max_new_tokens=64)
-    got = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=2, max_generate_length=48,
-                             repetition_penalty=2.0)
-    same = (got.cpu() == ref["codes"]).float().mean().item()
-    print("free-running greedy identical fraction", same)
-    assert same >= 0.99
+    got = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=2, max_generate_length=steps,
+                             repetition_penalty=2.0).cpu()
+    ids = torch.full((4, 16), 1, dtype=torch.long)
+    ids[:, -1] = cfg.start_mel_token
+    n_same = 0
+    for r in range(4):
+        diff = (got[r] != ref["codes"][r]).nonzero()
+        k = int(diff[0]) if len(diff) else steps
+        n_same += k
+        if k < steps:        # the oracle's processed scores at step k (history identical up to k)
+            hist = torch.cat([ids[r], ref["codes"][r, :k]])[None]
+            sc = apply_repetition_penalty(ref["logits"][k][r][None].clone(), hist, 2.0)[0]
+            top2 = torch.topk(sc, 2).values
+            gap = (top2[0] - top2[1]).item() / ref["logits"][k][r].abs().max().item()
+            assert gap < BF16_REL, (r, k, gap)
+            assert int(got[r, k]) in torch.topk(sc, 2).indices.tolist()
+    print("free-running greedy: identical prefix fraction", n_same / (4 * steps))
+    assert n_same / (4 * steps) >= 0.5
     m.close()
 
 
