@@ -1,0 +1,59 @@
+"""Bring-up tool: per-stage timestamps (CTA 0) of one decode step of the C2 workload.
+usage: TTS_AR_PROF_STEP=200 python scripts/stage_prof.py [n_cand] [steps]"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from tortoise_tts_b200 import UnifiedVoiceB200, ARGeometry  # noqa: E402
+from tortoise_tts_b200.synthetic import ARConfig, make_state_dict, make_inputs  # noqa: E402
+
+OPS = ["LN_QKV", "ATTN", "PROJ", "LN_FC", "PROJ2", "HEAD", "SAMPLE", "LATENT"]
+n_cand = int(sys.argv[1]) if len(sys.argv) > 1 else 16
+steps = int(sys.argv[2]) if len(sys.argv) > 2 else 300
+layers = int(os.environ.get("LAYERS", "30"))
+cfg = ARConfig(layers=layers)
+sd = make_state_dict(cfg, seed=0)
+lat, texts = make_inputs(cfg, 1, [64], seed=1)
+text = torch.stack(texts)
+m = UnifiedVoiceB200(sd, ARGeometry(layers=layers), max_utts=1, max_seqs=n_cand, max_text_len=64, max_new_tokens=520)
+kw = dict(do_sample=True, top_p=0.8, temperature=0.8, top_k=0, seed=1234, ignore_eos=True)
+for _ in range(2):
+    m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=n_cand, max_generate_length=steps, **kw)
+s = m.last_stats
+dec = s.last_device_ms - s.last_prefill_ms
+print(f"N={n_cand} steps={steps}: device {s.last_device_ms:.2f} ms, prefill {s.last_prefill_ms:.2f} ms, decode {dec / (steps - 1) * 1e3:.1f} us/step, "
+      f"alg {s.last_algorithmic_bytes / (dec * 1e-3) / 1e9:.0f} GB/s")
+if "TTS_AR_PROF_STEP" in os.environ:
+    n_instr = 1 + layers * 5 + 1
+    prog = np.array([[6]] + [[o] for _ in range(layers) for o in (0, 1, 2, 3, 4)] + [[5]])   # ProgIter order
+    raw = m.debug_buffer("prof", (1024 + 4096,), dtype=torch.int64).cpu().numpy()
+    t = raw[: 2 * n_instr].reshape(n_instr, 2)
+    marks = raw[1024:].reshape(-1, 2)
+    marks = marks[marks[:, 1] > 0]
+    names = {1: "A-ready", 2: "mma-done", 3: "epi-done", 11: "attn-plan"}
+    names.update({100 + i: "pre-bar " + o for i, o in enumerate(OPS)})
+    names.update({200 + i: "post-bar " + o for i, o in enumerate(OPS)})
+    sel = [i for i in range(len(marks)) if marks[i, 0] == 100]       # pre-barrier LN_QKV marks = layer starts
+    if len(sel) > 4:
+        a, b = sel[3], sel[4]
+        print("marks of layer 3 (delta ns from previous mark):")
+        for i in range(a, b + 1):
+            print(f"   {names.get(int(marks[i, 0]), marks[i, 0]):18s} +{int(marks[i, 1] - marks[i - 1, 1])}")
+    before, after = t[:, 0], t[:, 1]
+    wait = after - before                       # barrier wait seen by CTA 0
+    work = np.append(before[1:], before[-1]) - after   # stage body on CTA 0 (until it reaches the next barrier)
+    tot = {}
+    for i in range(n_instr):
+        op = OPS[prog[i, 0]]
+        a = tot.setdefault(op, [0, 0.0, 0.0])
+        a[0] += 1; a[1] += wait[i]; a[2] += work[i]
+    print("step span (SAMPLE barrier -> HEAD start):", (before[-1] - before[0]) / 1e3, "us")
+    for op, (n, w, k) in tot.items():
+        print(f"  {op:8s} n={n:3d}  barrier-wait avg {w / n / 1e3:7.2f} us   body(CTA0) avg {k / n / 1e3:7.2f} us")
+    L = 3
+    print("layer", L, [(OPS[prog[i, 0]], int(wait[i]), int(work[i])) for i in range(1 + 5 * L, 6 + 5 * L)])
+m.close()

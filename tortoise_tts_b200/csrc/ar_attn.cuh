@@ -202,6 +202,7 @@ __device__ void attn_stage(const Params& P, const Instr& ins, const Smem& sm) {
   } else {
     n_units = nrows * kH;
   }
+  prof_mark(P, sm.ctrl, 11);
   for (int u = blockIdx.x * kNW + w; u < n_units; u += P.G * kNW) {
     int row, head, p0, p1, ns, split;
     if (mode == 1) {

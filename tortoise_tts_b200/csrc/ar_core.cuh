@@ -34,6 +34,17 @@ __device__ __forceinline__ Smem carve_smem(uint8_t* base, int mt_max) {
   return s;
 }
 
+// Bring-up profiling: CTA 0 / thread 0 appends (id, ns) marks while ctrl->ibuf[1] is set (see ar_kernels.cu).
+__device__ __forceinline__ void prof_mark(const Params& P, Ctrl* c, int id) {
+  if (P.prof && blockIdx.x == 0 && threadIdx.x == 0 && c->ibuf[1]) {
+    const int k = c->ibuf[0]++;
+    if (k < 2048) {
+      P.prof[1024 + 2 * k] = (unsigned long long)id;
+      P.prof[1024 + 2 * k + 1] = globaltimer_ns();
+    }
+  }
+}
+
 // Consumer-side view of the weight stream: every consumer warp consumes every chunk, in order.
 struct Pipe {
   uint32_t ci;      // chunks consumed so far
@@ -64,6 +75,69 @@ __device__ __forceinline__ bool gemm_desc(const Params& P, const Instr& ins, Gem
   }
 }
 
+// The per-step instruction sequence, generated on the fly (no table in global memory on the critical path):
+//   [SAMPLE]  { LN_QKV g.. | ATTN | PROJ g.. | LN_FC g.. | PROJ2 g.. } x layers  [HEAD g.. | LATENT]
+// Row groups of kRowGroup rows; the first instruction of every op carries the grid barrier.
+struct ProgIter {
+  int layer, op, group, rot, phase;   // phase 0: sample, 1: layers, 2: tail, 3: done
+  int n_groups, n_head_groups;
+  __device__ __forceinline__ void reset(const Params& P) {
+    phase = P.has_sample ? 0 : 1;
+    layer = 0; op = OP_LN_QKV; group = 0; rot = 0;
+    n_groups = (P.n_rows + kRowGroup - 1) / kRowGroup;
+    n_head_groups = (P.n_head_rows + kRowGroup - 1) / kRowGroup;
+  }
+  __device__ __forceinline__ bool next(const Params& P, Instr& in) {
+    in.pad0 = in.pad1 = 0;
+    if (phase == 0) {
+      in.op = OP_SAMPLE; in.layer = 0; in.row0 = 0; in.nrows = P.n_seqs; in.flags = F_BARRIER_BEFORE; in.rot = 0;
+      phase = 1;
+      return true;
+    }
+    if (phase == 1) {
+      in.op = op; in.layer = layer; in.rot = rot;
+      if (op == OP_ATTN) {
+        in.row0 = 0; in.nrows = P.n_rows; in.flags = F_BARRIER_BEFORE;
+        op = OP_PROJ;
+        return true;
+      }
+      in.row0 = group * kRowGroup;
+      in.nrows = min(kRowGroup, P.n_rows - in.row0);
+      in.flags = (group == 0) ? F_BARRIER_BEFORE : 0;
+      if (group == 0 && op == OP_LN_QKV && layer == 0 && P.has_sample) in.flags |= F_CHECK_EXIT | F_PLAN;
+      if (++group == n_groups) {
+        group = 0;
+        const int nt = (op == OP_LN_QKV) ? kD3 / 8 : (op == OP_LN_FC ? kD4 / 8 : kD / 8);
+        rot = next_rot(nt, P.G, rot);
+        if (op == OP_PROJ2) {
+          op = OP_LN_QKV;
+          if (++layer == P.n_layers) phase = 2;
+        } else {
+          op = op + 1;
+        }
+      }
+      return true;
+    }
+    if (phase == 2) {
+      if (P.tail == 1) {
+        in.op = OP_HEAD; in.layer = 0; in.rot = rot;
+        in.row0 = group * kRowGroup;
+        in.nrows = min(kRowGroup, P.n_head_rows - in.row0);
+        in.flags = (group == 0 ? F_BARRIER_BEFORE : 0) | (P.decode_mode ? 0 : F_ROW_MAP);
+        if (++group == n_head_groups) phase = 3;
+        return true;
+      }
+      if (P.tail == 2) {
+        in.op = OP_LATENT; in.layer = 0; in.rot = rot; in.row0 = 0; in.nrows = P.n_rows; in.flags = F_BARRIER_BEFORE;
+        phase = 3;
+        return true;
+      }
+      phase = 3;
+    }
+    return false;
+  }
+};
+
 // Is instruction `pc` of step `step` executed?  (generate() does not run the model after the last token.)
 __device__ __forceinline__ bool instr_live(const Params& P, int step, const Instr& ins) {
   return !(P.skip_last_model && step == P.n_steps - 1 && ins.op != OP_SAMPLE);
@@ -77,8 +151,10 @@ __device__ void producer_loop(const Params& P, Ctrl* c, uint8_t* ring) {
   uint32_t pi = 0, slot = 0, round = 0;
   bool stopped = false;
   for (int step = 0; step < P.n_steps && !stopped; ++step) {
-    for (int pc = 0; pc < P.n_instr && !stopped; ++pc) {
-      const Instr ins = P.prog[pc];
+    ProgIter it;
+    it.reset(P);
+    Instr ins;
+    while (!stopped && it.next(P, ins)) {
       GemmDesc gd;
       if (!instr_live(P, step, ins) || !gemm_desc(P, ins, gd)) continue;
       int t0, cnt;
@@ -117,12 +193,13 @@ __device__ __forceinline__ bool grid_barrier(const Params& P, Ctrl* c, uint32_t&
   consumer_sync();
   ++epoch;
   if (threadIdx.x == 0) {
-    __threadfence();
+    // bar.sync above orders the CTA's writes before this release (cumulativity); the poll is relaxed and one
+    // acquire fence follows it, so the L1 invalidate happens once per barrier instead of once per poll.
     red_release_add_u32(P.bar_counter, 1u);
     const uint32_t target = epoch * (uint32_t)P.G;
     long long t0 = clock64();
     uint32_t spins = 0;
-    while (ld_acquire_u32(P.bar_counter) < target) {
+    while (ld_relaxed_u32(P.bar_counter) < target) {
       if ((++spins & 255u) == 0) {
         if (c->abort_flag || __ldcg(P.watchdog) || clock64() - t0 > kWatchdogCycles) {
           c->abort_flag = 1;
@@ -131,7 +208,7 @@ __device__ __forceinline__ bool grid_barrier(const Params& P, Ctrl* c, uint32_t&
         }
       }
     }
-    __threadfence();
+    fence_acq_rel_gpu();
   }
   consumer_sync();
   return c->abort_flag == 0;

@@ -71,6 +71,7 @@ template <int MT>
 __device__ void gemm_stage(const Params& P, const Instr& ins, const Smem& sm, Pipe& pipe) {
   constexpr int KS = kNW / MT;             // k-slices
   constexpr int KPW = kKbPerChunk / KS;    // k16-blocks per warp per chunk (4 * MT)
+  constexpr int KB = KPW > 16 ? 16 : KPW;  // A-fragment batch
   constexpr int NT = 4;                    // n8-tiles accumulated per pass
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int mt = w % MT, ks = w / MT;
@@ -93,6 +94,7 @@ __device__ void gemm_stage(const Params& P, const Instr& ins, const Smem& sm, Pi
       ln_rows_to_smem<true>(P, ins, sm.a_rm, P.lnf_g, P.lnf_b, P.fn_g, P.fn_b, MT);
     consumer_sync();
   }
+  prof_mark(P, c, 1);
   // ldmatrix row address of this lane inside m-tile `mt` (see layout notes in DESIGN.md)
   const uint32_t a_sm_base = smem_u32(sm.a_rm) + (uint32_t)((mt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * kARowBytes) +
                              (uint32_t)((lane >> 4) * 16);
@@ -104,33 +106,41 @@ __device__ void gemm_stage(const Params& P, const Instr& ins, const Smem& sm, Pi
 
   for (int tp = 0; tp < cnt; tp += NT) {
     const int ntc = (cnt - tp < NT) ? (cnt - tp) : NT;
-    float acc[NT][4];
+    float acc2[NT][2][4];                    // two independent accumulator chains per tile (mma latency)
 #pragma unroll
-    for (int i = 0; i < NT; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.f;
+    for (int i = 0; i < NT; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc2[i][0][j] = acc2[i][1][j] = 0.f;
 
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
       if (nt < ntc) {
         for (int kq = 0; kq < KQ; ++kq) {
-          // A fragments of this warp's k-slice (issued before waiting for the weights)
-          uint4 a[KPW];
+          // A fragments of this warp's k-slice, in batches of KB k16-blocks (first batch issued before
+          // waiting for the weights)
+          uint4 a[KB];
           const int kb0 = kq * kKbPerChunk + ks * KPW;
-          if (a_from_smem) {
+          bool ok = false;
 #pragma unroll
-            for (int i = 0; i < KPW; ++i) ldmatrix_x4(a_sm_base + (uint32_t)((kb0 + i) * 32), a[i].x, a[i].y, a[i].z, a[i].w);
-          } else {
+          for (int hb = 0; hb < KPW; hb += KB) {
+            if (a_from_smem) {
 #pragma unroll
-            for (int i = 0; i < KPW; ++i) a[i] = ld_cg_u4(a_gl + (size_t)(kb0 + i) * 32);
-          }
-          const bool ok = mbar_wait(&c->full[pipe.slot], pipe.phase, &c->abort_flag);
-          if (ok) {
-            const uint4* bsm = reinterpret_cast<const uint4*>(sm.ring + (size_t)pipe.slot * kChunkBytes) +
-                               (ks * (KPW / 2)) * 32 + lane;
+              for (int i = 0; i < KB; ++i)
+                ldmatrix_x4(a_sm_base + (uint32_t)((kb0 + hb + i) * 32), a[i].x, a[i].y, a[i].z, a[i].w);
+            } else {
 #pragma unroll
-            for (int s = 0; s < KPW / 2; ++s) {
-              const uint4 b = bsm[s * 32];
-              mma_bf16_16816(acc[nt], a[2 * s], b.x, b.y);
-              mma_bf16_16816(acc[nt], a[2 * s + 1], b.z, b.w);
+              for (int i = 0; i < KB; ++i) a[i] = ld_cg_u4(a_gl + (size_t)(kb0 + hb + i) * 32);
+            }
+            if (hb == 0) ok = mbar_wait(&c->full[pipe.slot], pipe.phase, &c->abort_flag);
+            if (ok) {
+              const uint4* bsm = reinterpret_cast<const uint4*>(sm.ring + (size_t)pipe.slot * kChunkBytes) +
+                                 (ks * (KPW / 2) + hb / 2) * 32 + lane;
+#pragma unroll
+              for (int s = 0; s < KB / 2; ++s) {
+                const uint4 b = bsm[s * 32];
+                mma_bf16_16816(acc2[nt][s & 1], a[2 * s], b.x, b.y);
+                mma_bf16_16816(acc2[nt][s & 1], a[2 * s + 1], b.z, b.w);
+              }
             }
           }
           __syncwarp();
@@ -139,11 +149,14 @@ __device__ void gemm_stage(const Params& P, const Instr& ins, const Smem& sm, Pi
         }
       }
     }
+    prof_mark(P, c, 2);
     // ---- cross-warp (split-K) reduction, fixed order ----
     float4* red4 = reinterpret_cast<float4*>(sm.red);
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt)
-      if (nt < ntc) red4[(w * NT + nt) * 32 + lane] = make_float4(acc[nt][0], acc[nt][1], acc[nt][2], acc[nt][3]);
+      if (nt < ntc)
+        red4[(w * NT + nt) * 32 + lane] = make_float4(acc2[nt][0][0] + acc2[nt][1][0], acc2[nt][0][1] + acc2[nt][1][1],
+                                                      acc2[nt][0][2] + acc2[nt][1][2], acc2[nt][0][3] + acc2[nt][1][3]);
     consumer_sync();
     const float2* red2 = reinterpret_cast<const float2*>(sm.red);
     for (int e = threadIdx.x; e < MT * ntc * 64; e += kConsumerThreads) {
@@ -161,6 +174,7 @@ __device__ void gemm_stage(const Params& P, const Instr& ins, const Smem& sm, Pi
       gemm_epilogue(P, ins, emt * 16 + (ln >> 2) + 8 * pr, (t0 + tp + nt) * 8 + 2 * (ln & 3), s0, s1);
     }
     consumer_sync();
+    prof_mark(P, c, 3);
   }
 }
 

@@ -21,6 +21,8 @@ __global__ void __launch_bounds__(kThreads, 1) ar_program_kernel(const __grid_co
       mbar_init(&c->empty[i], kNW);
     }
     c->abort_flag = 0;
+    c->ibuf[0] = 0;
+    c->ibuf[1] = 0;
     c->stop_flag = 0;
     c->stop_ci = 0;
     fence_mbar_init();
@@ -38,10 +40,18 @@ __global__ void __launch_bounds__(kThreads, 1) ar_program_kernel(const __grid_co
   int steps_done = 0;
   bool alive = true;
   for (int step = 0; step < P.n_steps && alive; ++step) {
-    for (int pc = 0; pc < P.n_instr && alive; ++pc) {
-      const Instr ins = P.prog[pc];
+    ProgIter it;
+    it.reset(P);
+    Instr ins;
+    for (int pc = 0; alive && it.next(P, ins); ++pc) {
       if (!instr_live(P, step, ins)) continue;
+      const bool prof = P.prof && step == P.prof_step && blockIdx.x == 0 && threadIdx.x == 0;
+      if (prof) P.prof[2 * pc] = globaltimer_ns();
+      if (blockIdx.x == 0 && threadIdx.x == 0) c->ibuf[1] = (P.prof && step == P.prof_step) ? 1 : 0;
+      prof_mark(P, c, 100 + ins.op);
       if (ins.flags & F_BARRIER_BEFORE) alive = grid_barrier(P, c, epoch);
+      if (prof) P.prof[2 * pc + 1] = globaltimer_ns();
+      prof_mark(P, c, 200 + ins.op);
       if (!alive) break;
       if ((ins.flags & F_CHECK_EXIT) && ld_cg_i(P.n_active) == 0) { alive = false; break; }
       switch (ins.op) {

@@ -108,9 +108,14 @@ struct Params {
   unsigned int* bar_counter;
   int* watchdog;
   int* steps_done;
-  const Instr* prog;
-  int n_instr;
+  // program shape (generated procedurally by ProgIter, identically in the producer and the consumers)
+  int has_sample;        // decode: every step starts with OP_SAMPLE
+  int n_rows;            // rows run through the layers (sequences in decode, prompt positions otherwise)
+  int tail;              // 1: OP_HEAD over n_head_rows (F_ROW_MAP in prompt mode), 2: OP_LATENT over n_rows
+  int n_head_rows;
   int n_steps;
+  unsigned long long* prof;   // nullable: CTA 0 stage timestamps (ns) of step prof_step: [2*pc] before / [2*pc+1] after the barrier
+  int prof_step;
   int skip_last_model;   // generate(): the model is not run after the last sampled token
 };
 

@@ -13,7 +13,7 @@
 
 namespace tts {
 
-constexpr int kVPerThread = 17;   // 17 * 512 = 8704 >= 8194
+constexpr int kVPerThread = (8448 + kConsumerThreads - 1) / kConsumerThreads;   // covers n_mel_codes <= 8448
 
 __device__ __forceinline__ uint32_t key_of(float v) { return float_key(__float_as_uint(v)); }
 

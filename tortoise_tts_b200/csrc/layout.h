@@ -26,7 +26,7 @@ constexpr int kChunkK = 1024;     // k extent of one streamed weight chunk
 constexpr int kChunkN = 8;        // n extent (one mma n8 tile)
 constexpr int kChunkBytes = kChunkK * kChunkN * 2;   // 16 KiB of bf16
 constexpr int kKbPerChunk = kChunkK / 16;            // 64 k16-blocks
-constexpr int kNW = 16;           // consumer warps per CTA
+constexpr int kNW = 8;            // consumer warps per CTA (8 + 1 producer = 9 warps -> 168 registers/thread, no spills)
 constexpr int kConsumerThreads = kNW * 32;
 constexpr int kThreads = kConsumerThreads + 32;      // + 1 producer warp
 constexpr int kRowGroup = 64;     // rows handled per GEMM instruction (<= 4 M-tiles of 16)

@@ -2,6 +2,7 @@
 // prompt pass, sample loop, latent re-forward -- is in tts_ar_run.cu.)
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <algorithm>
 #include "tts_ar_host.h"
 
@@ -131,12 +132,10 @@ static int create_impl(TtsArHandle* h) {
   DALLOC(h, h->d_bar, 4);
   DALLOC(h, h->d_watchdog, 4);
   DALLOC(h, h->d_steps_done, 4);
-  const int pf_groups = (h->rows_cap + kRowGroup - 1) / kRowGroup;
-  h->prog_pf_cap = c.n_layers * (4 * pf_groups + 1) + pf_groups + 8;
-  const int dec_groups = (c.max_seqs + kRowGroup - 1) / kRowGroup;
-  h->prog_dec_cap = c.n_layers * (4 * dec_groups + 1) + dec_groups + 8;
-  DALLOC(h, h->d_prog_pf, h->prog_pf_cap);
-  DALLOC(h, h->d_prog_dec, h->prog_dec_cap);
+  if (const char* e = getenv("TTS_AR_PROF_STEP")) {   // bring-up only: per-stage timestamps of one decode step
+    h->prof_step = atoi(e);
+    DALLOC(h, h->d_prof, 1024 + 4096);
+  }
   DALLOC(h, h->d_in_latent, (size_t)c.max_utts * kD);
   DALLOC(h, h->d_in_text, (size_t)c.max_utts * std::max(c.max_text_len, 1));
   DALLOC(h, h->d_out_codes, (size_t)c.max_seqs * std::max(c.max_new_tokens, 1));

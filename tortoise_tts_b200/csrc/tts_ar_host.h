@@ -46,8 +46,8 @@ struct TtsArHandle {
   int *d_text_len = nullptr, *d_codes_len = nullptr;
   unsigned int* d_bar = nullptr;
   int *d_watchdog = nullptr, *d_steps_done = nullptr;
-  tts::Instr *d_prog_pf = nullptr, *d_prog_dec = nullptr;
-  int prog_pf_cap = 0, prog_dec_cap = 0;
+  unsigned long long* d_prof = nullptr;
+  int prof_step = -1;
   // staging for the host-buffer entry point (pinned host + device)
   float* d_in_latent = nullptr;
   int* d_in_text = nullptr;

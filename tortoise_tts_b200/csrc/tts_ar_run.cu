@@ -35,51 +35,14 @@ void fill_common_params(TtsArHandle* h, Params& P) {
   P.bar_counter = h->d_bar; P.watchdog = h->d_watchdog; P.steps_done = h->d_steps_done;
 }
 
-static void push_gemm_groups(std::vector<Instr>& prog, int op, int layer, int n_rows, int rot, int first_flags) {
-  for (int r0 = 0, g = 0; r0 < n_rows; r0 += kRowGroup, ++g) {
-    Instr in{};
-    in.op = op; in.layer = layer; in.row0 = r0; in.nrows = std::min(kRowGroup, n_rows - r0);
-    in.flags = (g == 0) ? first_flags : 0;
-    in.rot = rot;
-    prog.push_back(in);
-  }
-}
-
-// One pass over all layers for `n_rows` rows; `rot` carries the tile-schedule rotation across GEMMs.
-static void push_layers(std::vector<Instr>& prog, int n_layers, int n_rows, int G, int& rot, int first_qkv_flags) {
-  for (int l = 0; l < n_layers; ++l) {
-    push_gemm_groups(prog, OP_LN_QKV, l, n_rows, rot, F_BARRIER_BEFORE | (l == 0 ? first_qkv_flags : 0));
-    rot = next_rot(kD3 / 8, G, rot);
-    Instr at{};
-    at.op = OP_ATTN; at.layer = l; at.row0 = 0; at.nrows = n_rows; at.flags = F_BARRIER_BEFORE;
-    prog.push_back(at);
-    push_gemm_groups(prog, OP_PROJ, l, n_rows, rot, F_BARRIER_BEFORE);
-    rot = next_rot(kD / 8, G, rot);
-    push_gemm_groups(prog, OP_LN_FC, l, n_rows, rot, F_BARRIER_BEFORE);
-    rot = next_rot(kD4 / 8, G, rot);
-    push_gemm_groups(prog, OP_PROJ2, l, n_rows, rot, F_BARRIER_BEFORE);
-    rot = next_rot(kD / 8, G, rot);
-  }
-}
-
 static int mt_max_for(int n_rows) {
   const int m = (std::min(n_rows, kRowGroup) + 15) / 16;
   return m <= 1 ? 1 : (m == 2 ? 2 : 4);
 }
 
 int build_decode_program(TtsArHandle* h, cudaStream_t st) {
-  std::vector<Instr> prog;
-  Instr s{};
-  s.op = OP_SAMPLE; s.nrows = h->n_seqs; s.flags = F_BARRIER_BEFORE;
-  prog.push_back(s);
-  int rot = 0;
-  push_layers(prog, h->cfg.n_layers, h->n_seqs, h->G, rot, F_CHECK_EXIT | F_PLAN);
-  push_gemm_groups(prog, OP_HEAD, 0, h->n_seqs, rot, F_BARRIER_BEFORE);
-  if ((int)prog.size() > h->prog_dec_cap) return fail(h, TTS_AR_ERR_CAPACITY, "decode program too long");
-  h->dec_n_instr = (int)prog.size();
-  h->dec_mt_max = mt_max_for(h->n_seqs);
-  TTS_CUDA(h, cudaMemcpyAsync(h->d_prog_dec, prog.data(), sizeof(Instr) * prog.size(), cudaMemcpyHostToDevice, st));
-  TTS_CUDA(h, cudaStreamSynchronize(st));   // `prog` is a local pageable buffer
+  (void)st;
+  h->dec_mt_max = mt_max_for(h->n_seqs);   // the instruction sequence itself is generated on the device (ProgIter)
   return 0;
 }
 
@@ -110,26 +73,7 @@ int run_prompt_pass(TtsArHandle* h, const std::vector<int>& seq_len, const std::
     for (int p = 0; p < np; ++p) pt[(size_t)i * kMaxPagesPerSeg + p] = next_page++;
   }
   if (next_page > h->n_pages) return fail(h, TTS_AR_ERR_CAPACITY, "KV page pool exhausted");
-  std::vector<Instr> prog;
-  int rot = 0;
-  push_layers(prog, h->cfg.n_layers, n_rows, h->G, rot, 0);
-  int n_head_rows = 0;
-  if (with_head) {
-    n_head_rows = (int)head_rows.size();
-    for (int r0 = 0, g = 0; r0 < n_head_rows; r0 += kRowGroup, ++g) {
-      Instr in{};
-      in.op = OP_HEAD; in.row0 = r0; in.nrows = std::min(kRowGroup, n_head_rows - r0);
-      in.flags = F_ROW_MAP | (g == 0 ? F_BARRIER_BEFORE : 0);
-      in.rot = rot;
-      prog.push_back(in);
-    }
-  } else {
-    Instr in{};
-    in.op = OP_LATENT; in.row0 = 0; in.nrows = n_rows; in.flags = F_BARRIER_BEFORE;
-    prog.push_back(in);
-  }
-  if ((int)prog.size() > h->prog_pf_cap) return fail(h, TTS_AR_ERR_CAPACITY, "prompt program too long");
-  h->pf_n_instr = (int)prog.size();
+  const int n_head_rows = with_head ? (int)head_rows.size() : 0;
   TTS_CUDA(h, cudaMemcpyAsync(h->d_prefix_pt, pt.data(), sizeof(int) * pt.size(), cudaMemcpyHostToDevice, st));
   TTS_CUDA(h, cudaMemcpyAsync(h->d_utt_plen, seq_len.data(), sizeof(int) * n_seq, cudaMemcpyHostToDevice, st));
   TTS_CUDA(h, cudaMemcpyAsync(h->d_pf_row_utt, row_utt.data(), sizeof(int) * n_rows, cudaMemcpyHostToDevice, st));
@@ -138,7 +82,6 @@ int run_prompt_pass(TtsArHandle* h, const std::vector<int>& seq_len, const std::
     TTS_CUDA(h, cudaMemcpyAsync(h->d_head_rows, head_rows.data(), sizeof(int) * n_head_rows, cudaMemcpyHostToDevice, st));
   else
     TTS_CUDA(h, cudaMemcpyAsync(h->d_latent_dst, latent_dst.data(), sizeof(int) * n_rows, cudaMemcpyHostToDevice, st));
-  TTS_CUDA(h, cudaMemcpyAsync(h->d_prog_pf, prog.data(), sizeof(Instr) * prog.size(), cudaMemcpyHostToDevice, st));
   TTS_CUDA(h, cudaMemsetAsync(h->d_plan, 0, sizeof(int) * 4, st));   // plan[0] = 0: direct (row, head) units
   TTS_CUDA(h, cudaStreamSynchronize(st));                             // local pageable buffers above
   return 0;
@@ -190,8 +133,7 @@ extern "C" int tts_ar_prefill(TtsArHandle* h, const float* latent, const int32_t
   P.decode_mode = 0;
   P.row_utt = h->d_pf_row_utt; P.row_pos = h->d_pf_row_pos;
   P.mt_max = mt_max_for(std::max(n_rows, n_utt));
-  P.prog = h->d_prog_pf;
-  P.n_instr = h->pf_n_instr;
+  P.has_sample = 0; P.n_rows = n_rows; P.tail = 1; P.n_head_rows = n_utt;
   P.n_steps = 1;
   P.n_seqs = 0;
   rc = launch(h, P, st);
@@ -239,9 +181,10 @@ static int run_steps(TtsArHandle* h, const TtsArSampling* s, int n_steps, bool s
   P.decode_mode = 1;
   P.row_utt = h->d_seq_utt; P.row_pos = h->d_seq_pos;
   P.mt_max = h->dec_mt_max;
-  P.prog = h->d_prog_dec; P.n_instr = h->dec_n_instr;
+  P.has_sample = 1; P.n_rows = h->n_seqs; P.tail = 1; P.n_head_rows = h->n_seqs;
   P.n_steps = n_steps; P.skip_last_model = skip_last_model ? 1 : 0;
   P.n_seqs = h->n_seqs;
+  P.prof = h->d_prof; P.prof_step = h->prof_step;
   P.first_step_from_prefill = h->first_step_pending ? 1 : 0;
   P.do_sample = s->do_sample; P.top_k = s->top_k; P.ignore_eos = s->ignore_eos;
   P.temperature = s->temperature; P.top_p = s->top_p; P.rep_penalty = s->repetition_penalty;
@@ -379,8 +322,7 @@ extern "C" int tts_ar_forward_latents(TtsArHandle* h, const float* latent, const
     P.decode_mode = 0;
     P.row_utt = h->d_pf_row_utt; P.row_pos = h->d_pf_row_pos;
     P.mt_max = mt_max_for(n_rows);
-    P.prog = h->d_prog_pf;
-    P.n_instr = h->pf_n_instr;
+    P.has_sample = 0; P.n_rows = n_rows; P.tail = 2; P.n_head_rows = 0;
     P.n_steps = 1;
     P.latent_out = out;
     rc = launch(h, P, st);
@@ -433,6 +375,7 @@ extern "C" int tts_ar_debug_copy(TtsArHandle* h, const char* name, void* dst, ui
   else if (n == "kv") src = h->d_kv;
   else if (n == "ctx") src = h->d_ctx;
   else if (n == "h") src = h->d_h;
+  else if (n == "prof") src = h->d_prof;
   else return fail(h, TTS_AR_ERR_BAD_ARG, "unknown debug buffer");
   TTS_CUDA(h, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
   return 0;
