@@ -13,5 +13,6 @@ long long lc_kv_row_offset(int layer, int n_pages, int page, int kv, int head, i
 void lc_tile_range(int n_tiles, int G, int rot, int cta, int* t0, int* cnt) { tts::tile_range(n_tiles, G, rot, cta, t0, cnt); }
 int lc_next_rot(int n_tiles, int G, int rot) { return tts::next_rot(n_tiles, G, rot); }
 unsigned lc_float_key(unsigned bits) { return tts::float_key(bits); }
+int lc_projk_elem_offset(int k, int n) { return tts::projk_elem_offset(k, n); }
 int lc_chunk_bytes(void) { return tts::kChunkBytes; }
 }

@@ -20,7 +20,7 @@ __device__ __forceinline__ void write_ctx_pair(const Params& P, int row, int col
 // Builds the decode split plan for rows [0, nrows): executed by ONE warp.
 //   plan[0] = 1 (split mode)  plan[1] = n_units  plan[2] = tp  plan[4 + r] = first unit of row r (nrows + 1 entries)
 // Row r gets ns_r = min(32, ceil(kvlen_r / tp)) splits; its units are [split][head].
-__device__ void build_attn_plan(const Params& P, int nrows) {
+static __device__ void build_attn_plan(const Params& P, int nrows) {
   const int lane = threadIdx.x & 31;
   int total = 0, maxlen = 0;
   for (int r = lane; r < nrows; r += 32) {
@@ -188,7 +188,7 @@ __device__ __forceinline__ void attn_combine(const Params& P, int row, int head,
   write_ctx_pair(P, row, head * kHD + 2 * lane, o0 * inv, o1 * inv);
 }
 
-__device__ void attn_stage(const Params& P, const Instr& ins, const Smem& sm) {
+static __device__ void attn_stage(const Params& P, const Instr& ins, const Smem& sm) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int rg = lane >> 3, dc = lane & 7;
   const int mode = ld_cg_i(P.plan + 0);

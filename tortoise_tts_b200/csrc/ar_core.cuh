@@ -11,6 +11,7 @@ constexpr int kMaxSlots = 12;
 struct Ctrl {
   uint64_t full[kMaxSlots];    // producer -> consumers: chunk landed (tx-count barrier)
   uint64_t empty[kMaxSlots];   // consumers -> producer: slot free again (16 warp arrivals)
+  uint64_t cbar;               // cluster barrier (ar_decode.cu): one arrival per CTA of the cluster per phase
   float scratch[32];
   volatile int abort_flag;     // a wait timed out somewhere: fall through everything
   volatile int stop_flag;      // consumers are done (normal end or early exit)
@@ -144,7 +145,7 @@ __device__ __forceinline__ bool instr_live(const Params& P, int step, const Inst
 }
 
 // ---- producer warp: streams this CTA's weight chunks for the whole launch, ahead of the barriers --------
-__device__ void producer_loop(const Params& P, Ctrl* c, uint8_t* ring) {
+static __device__ void producer_loop(const Params& P, Ctrl* c, uint8_t* ring) {
   if ((threadIdx.x & 31) != 0) return;
   const uint64_t pol = make_evict_first_policy();
   const int cta = blockIdx.x;
@@ -215,87 +216,115 @@ __device__ __forceinline__ bool grid_barrier(const Params& P, Ctrl* c, uint32_t&
 }
 
 // ---- LayerNorm of up to 64 rows into the shared bf16 A operand ------------------------------------------------
-// Warp w normalises rows w, w+16, ... (fp32 statistics, two-pass, eps 1e-5 = nn.LayerNorm default used by
-// HF GPT2Block and by final_norm).  kDouble: ln_f then final_norm (reference quirk Q1,
-// unified_voice.py:106,239); CTA 0 also publishes the fp32 result as the step latent
-// (stream_generator.py:1172).  Rows >= nrows of the last M-tile are zero-filled.
-template <bool kDouble>
-__device__ void ln_rows_to_smem(const Params& P, const Instr& ins, uint8_t* a_rm, const float* g1, const float* b1,
-                                const float* g2, const float* b2, int mt_count) {
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  for (int r = w; r < mt_count * 16; r += kNW) {
-    uint8_t* dst = a_rm + (size_t)r * kARowBytes;
-    if (r >= ins.nrows) {
+// Warp w normalises rows w, w+8, ... two at a time (all loads of both rows are issued before the first
+// reduction; the gain/bias lines are prefetched into L1 up front, so a 16-row stage costs one L2 round trip).
+// fp32 statistics, two-pass, eps 1e-5 = nn.LayerNorm default used by HF GPT2Block and by final_norm.
+// kDouble: ln_f then final_norm (reference quirk Q1, unified_voice.py:106,239); CTA 0 also publishes the fp32
+// result as the step latent (stream_generator.py:1172).  Rows >= nrows of the last M-tile are zero-filled.
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
+__device__ __forceinline__ void ln_load_row(const Params& P, const Instr& ins, const float* src, int xrow, int lane, float4 (&v)[8]) {
+  if (ins.flags & F_FIXED_SRC) {
+    const long long* yp = P.y + (size_t)xrow * kD;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) *reinterpret_cast<uint2*>(dst + (128 * j + 4 * lane) * 2) = make_uint2(0u, 0u);
-      continue;
+    for (int j = 0; j < 8; ++j) {
+      const longlong2 a = ld_cg_ll2(yp + 128 * j + 4 * lane), b = ld_cg_ll2(yp + 128 * j + 4 * lane + 2);
+      v[j] = make_float4(from_fixed(a.x), from_fixed(a.y), from_fixed(b.x), from_fixed(b.y));
     }
-    const int lrow = ins.row0 + r;                                    // logical row (logits / latent row)
-    const int xrow = (ins.flags & F_ROW_MAP) ? P.head_rows[lrow] : lrow;
-    const float* xp = P.x + (size_t)xrow * kD;
-    float4 v[8];
+  } else {
+    const float* xp = src + (size_t)xrow * kD;
 #pragma unroll
     for (int j = 0; j < 8; ++j) v[j] = ld_cg_f4(xp + 128 * j + 4 * lane);
-    float s = 0.f;
+  }
+}
+
+__device__ __forceinline__ void ln_normalise(float4 (&v)[8], const float* g, const float* b, int lane) {
+  float s = 0.f;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
-    const float mean = warp_sum(s) * (1.0f / kD);
-    float ss = 0.f;
+  for (int j = 0; j < 8; ++j) s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
+  const float mean = warp_sum(s) * (1.0f / kD);
+  float ss = 0.f;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float a = v[j].x - mean, b = v[j].y - mean, c2 = v[j].z - mean, d = v[j].w - mean;
-      ss += (a * a + b * b) + (c2 * c2 + d * d);
+  for (int j = 0; j < 8; ++j) {
+    const float a = v[j].x - mean, bq = v[j].y - mean, c2 = v[j].z - mean, d = v[j].w - mean;
+    ss += (a * a + bq * bq) + (c2 * c2 + d * d);
+  }
+  const float rstd = rsqrtf(warp_sum(ss) * (1.0f / kD) + 1e-5f);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float4 gg = *reinterpret_cast<const float4*>(g + 128 * j + 4 * lane);
+    const float4 bb = *reinterpret_cast<const float4*>(b + 128 * j + 4 * lane);
+    v[j].x = (v[j].x - mean) * rstd * gg.x + bb.x;
+    v[j].y = (v[j].y - mean) * rstd * gg.y + bb.y;
+    v[j].z = (v[j].z - mean) * rstd * gg.z + bb.z;
+    v[j].w = (v[j].w - mean) * rstd * gg.w + bb.w;
+  }
+}
+
+template <bool kDouble>
+__device__ __forceinline__ void ln_finish_row(const Params& P, const Instr& ins, uint8_t* dst, int lrow, int lane, float4 (&v)[8],
+                                              const float* g1, const float* b1, const float* g2, const float* b2) {
+  ln_normalise(v, g1, b1, lane);
+  if (kDouble) {
+    ln_normalise(v, g2, b2, lane);
+    if (ins.op == OP_HEAD && blockIdx.x == 0) {
+      float* lp = P.cur_latent + (size_t)lrow * kD;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) *reinterpret_cast<float4*>(lp + 128 * j + 4 * lane) = v[j];
     }
-    const float rstd = rsqrtf(warp_sum(ss) * (1.0f / kD) + 1e-5f);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float4 g = *reinterpret_cast<const float4*>(g1 + 128 * j + 4 * lane);
-      const float4 b = *reinterpret_cast<const float4*>(b1 + 128 * j + 4 * lane);
-      v[j].x = (v[j].x - mean) * rstd * g.x + b.x;
-      v[j].y = (v[j].y - mean) * rstd * g.y + b.y;
-      v[j].z = (v[j].z - mean) * rstd * g.z + b.z;
-      v[j].w = (v[j].w - mean) * rstd * g.w + b.w;
-    }
-    if (kDouble) {
-      float s2 = 0.f;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) s2 += (v[j].x + v[j].y) + (v[j].z + v[j].w);
-      const float mean2 = warp_sum(s2) * (1.0f / kD);
-      float ss2 = 0.f;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float a = v[j].x - mean2, b = v[j].y - mean2, c2 = v[j].z - mean2, d = v[j].w - mean2;
-        ss2 += (a * a + b * b) + (c2 * c2 + d * d);
-      }
-      const float rstd2 = rsqrtf(warp_sum(ss2) * (1.0f / kD) + 1e-5f);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float4 g = *reinterpret_cast<const float4*>(g2 + 128 * j + 4 * lane);
-        const float4 b = *reinterpret_cast<const float4*>(b2 + 128 * j + 4 * lane);
-        v[j].x = (v[j].x - mean2) * rstd2 * g.x + b.x;
-        v[j].y = (v[j].y - mean2) * rstd2 * g.y + b.y;
-        v[j].z = (v[j].z - mean2) * rstd2 * g.z + b.z;
-        v[j].w = (v[j].w - mean2) * rstd2 * g.w + b.w;
-      }
-      if (ins.op == OP_HEAD && blockIdx.x == 0) {
-        float* lp = P.cur_latent + (size_t)lrow * kD;
+    if (ins.op == OP_LATENT) {
+      const int drow = P.latent_dst[lrow];
+      if (drow >= 0) {
+        float* lp = P.latent_out + (size_t)drow * kD;
 #pragma unroll
         for (int j = 0; j < 8; ++j) *reinterpret_cast<float4*>(lp + 128 * j + 4 * lane) = v[j];
       }
-      if (ins.op == OP_LATENT) {
-        const int drow = P.latent_dst[lrow];
-        if (drow >= 0) {
-          float* lp = P.latent_out + (size_t)drow * kD;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) *reinterpret_cast<float4*>(lp + 128 * j + 4 * lane) = v[j];
-        }
-      }
     }
-    if (ins.op != OP_LATENT) {
+  }
+  if (ins.op != OP_LATENT) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j)
-        *reinterpret_cast<uint2*>(dst + (128 * j + 4 * lane) * 2) =
-            make_uint2(pack_bf16x2(v[j].x, v[j].y), pack_bf16x2(v[j].z, v[j].w));
+    for (int j = 0; j < 8; ++j)
+      *reinterpret_cast<uint2*>(dst + (128 * j + 4 * lane) * 2) =
+          make_uint2(pack_bf16x2(v[j].x, v[j].y), pack_bf16x2(v[j].z, v[j].w));
+  }
+}
+
+template <bool kDouble>
+__device__ void ln_rows_to_smem(const Params& P, const Instr& ins, uint8_t* a_rm, const float* src, const float* g1, const float* b1,
+                                const float* g2, const float* b2, int mt_count) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  prefetch_l1(g1 + 32 * lane);
+  prefetch_l1(b1 + 32 * lane);
+  if (kDouble) {
+    prefetch_l1(g2 + 32 * lane);
+    prefetch_l1(b2 + 32 * lane);
+  }
+  for (int r0 = w; r0 < mt_count * 16; r0 += 2 * kNW) {
+    const int r1 = r0 + kNW;
+    const bool ok0 = r0 < ins.nrows, ok1 = r1 < ins.nrows;
+    float4 v0[8], v1[8];
+    int l0 = 0, l1 = 0;
+    if (ok0) {
+      l0 = ins.row0 + r0;                                   // logical row (logits / latent row)
+      ln_load_row(P, ins, src, (ins.flags & F_ROW_MAP) ? P.head_rows[l0] : l0, lane, v0);
+    }
+    if (ok1) {
+      l1 = ins.row0 + r1;
+      ln_load_row(P, ins, src, (ins.flags & F_ROW_MAP) ? P.head_rows[l1] : l1, lane, v1);
+    }
+    uint8_t* d0 = a_rm + (size_t)r0 * kARowBytes;
+    uint8_t* d1 = a_rm + (size_t)r1 * kARowBytes;
+    if (ok0) {
+      ln_finish_row<kDouble>(P, ins, d0, l0, lane, v0, g1, b1, g2, b2);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) *reinterpret_cast<uint2*>(d0 + (128 * j + 4 * lane) * 2) = make_uint2(0u, 0u);
+    }
+    if (ok1) {
+      ln_finish_row<kDouble>(P, ins, d1, l1, lane, v1, g1, b1, g2, b2);
+    } else if (r1 < mt_count * 16) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) *reinterpret_cast<uint2*>(d1 + (128 * j + 4 * lane) * 2) = make_uint2(0u, 0u);
     }
   }
 }

@@ -15,6 +15,7 @@ __device__ __forceinline__ void gemm_epilogue(const Params& P, const Instr& ins,
                                               float v1) {
   if (row_in_group >= ins.nrows) return;
   const int row = ins.row0 + row_in_group;
+  if ((ins.flags & F_ROW_RANGE) && (row < ins.pad0 || row >= ins.pad1)) return;
   switch (ins.op) {
     case OP_LN_QKV: {
       const float* bias = P.layers[ins.layer].b_qkv;
@@ -46,6 +47,13 @@ __device__ __forceinline__ void gemm_epilogue(const Params& P, const Instr& ins,
     case OP_PROJ2: {
       const float* bias = (ins.op == OP_PROJ) ? P.layers[ins.layer].b_proj : P.layers[ins.layer].b_proj2;
       float* xp = P.x + (size_t)row * kD + col;
+      if (P.y && ins.op == OP_PROJ2) {   // cluster decode kernel: x = y + mlp ; y is handed back zeroed
+        long long* yp = P.y + (size_t)row * kD + col;
+        const longlong2 old = ld_cg_ll2(yp);
+        *reinterpret_cast<float2*>(xp) = make_float2(from_fixed(old.x) + v0 + bias[col], from_fixed(old.y) + v1 + bias[col + 1]);
+        *reinterpret_cast<longlong2*>(yp) = make_longlong2(0ll, 0ll);
+        break;
+      }
       const float2 old = ld_cg_f2(xp);
       *reinterpret_cast<float2*>(xp) = make_float2(old.x + v0 + bias[col], old.y + v1 + bias[col + 1]);
       break;
@@ -67,8 +75,11 @@ __device__ __forceinline__ void gemm_epilogue(const Params& P, const Instr& ins,
 }
 
 // MT = M-tiles of 16 rows in this instruction (1, 2 or 4).  Warp w: m-tile w % MT, k-slice w / MT.
+// Tiles of this CTA: t0 + (i / tinner) * tstride + i % tinner, i < cnt (tinner >= cnt = the contiguous schedule
+// of tile_range).
 template <int MT>
-__device__ void gemm_stage(const Params& P, const Instr& ins, const Smem& sm, Pipe& pipe) {
+__device__ void gemm_tiles(const Params& P, const Instr& ins, const Smem& sm, Pipe& pipe, int t0, int cnt, int tstride,
+                           int tinner, const float* ln_src) {
   constexpr int KS = kNW / MT;             // k-slices
   constexpr int KPW = kKbPerChunk / KS;    // k16-blocks per warp per chunk (4 * MT)
   constexpr int KB = KPW > 16 ? 16 : KPW;  // A-fragment batch
@@ -79,19 +90,17 @@ __device__ void gemm_stage(const Params& P, const Instr& ins, const Smem& sm, Pi
 
   GemmDesc gd;
   gemm_desc(P, ins, gd);
-  int t0, cnt;
-  tile_range(gd.n_tiles, P.G, ins.rot, blockIdx.x, &t0, &cnt);
   const int KQ = gd.K / kChunkK;
   const bool a_from_smem = (ins.op == OP_LN_QKV || ins.op == OP_LN_FC || ins.op == OP_HEAD);
 
   // ---- A operand ----
   if (a_from_smem) {
     if (ins.op == OP_LN_QKV)
-      ln_rows_to_smem<false>(P, ins, sm.a_rm, P.layers[ins.layer].ln1_g, P.layers[ins.layer].ln1_b, nullptr, nullptr, MT);
+      ln_rows_to_smem<false>(P, ins, sm.a_rm, ln_src, P.layers[ins.layer].ln1_g, P.layers[ins.layer].ln1_b, nullptr, nullptr, MT);
     else if (ins.op == OP_LN_FC)
-      ln_rows_to_smem<false>(P, ins, sm.a_rm, P.layers[ins.layer].ln2_g, P.layers[ins.layer].ln2_b, nullptr, nullptr, MT);
+      ln_rows_to_smem<false>(P, ins, sm.a_rm, ln_src, P.layers[ins.layer].ln2_g, P.layers[ins.layer].ln2_b, nullptr, nullptr, MT);
     else
-      ln_rows_to_smem<true>(P, ins, sm.a_rm, P.lnf_g, P.lnf_b, P.fn_g, P.fn_b, MT);
+      ln_rows_to_smem<true>(P, ins, sm.a_rm, ln_src, P.lnf_g, P.lnf_b, P.fn_g, P.fn_b, MT);
     consumer_sync();
   }
   prof_mark(P, c, 1);
@@ -171,11 +180,20 @@ __device__ void gemm_stage(const Params& P, const Instr& ins, const Smem& sm, Pi
         s0 += v.x;
         s1 += v.y;
       }
-      gemm_epilogue(P, ins, emt * 16 + (ln >> 2) + 8 * pr, (t0 + tp + nt) * 8 + 2 * (ln & 3), s0, s1);
+      gemm_epilogue(P, ins, emt * 16 + (ln >> 2) + 8 * pr, (t0 + ((tp + nt) / tinner) * tstride + (tp + nt) % tinner) * 8 + 2 * (ln & 3), s0, s1);
     }
     consumer_sync();
     prof_mark(P, c, 3);
   }
+}
+
+template <int MT>
+__device__ void gemm_stage(const Params& P, const Instr& ins, const Smem& sm, Pipe& pipe) {
+  GemmDesc gd;
+  gemm_desc(P, ins, gd);
+  int t0, cnt;
+  tile_range(gd.n_tiles, P.G, ins.rot, blockIdx.x, &t0, &cnt);
+  gemm_tiles<MT>(P, ins, sm, pipe, t0, cnt, 0, 1 << 30, P.x);
 }
 
 }  // namespace tts

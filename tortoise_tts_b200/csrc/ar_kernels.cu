@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(kThreads, 1) ar_program_kernel(const __grid_co
             Instr sub = ins;
             sub.row0 = ins.row0 + rg * 16;
             sub.nrows = min(16, ins.nrows - rg * 16);
-            ln_rows_to_smem<true>(P, sub, sm.a_rm, P.lnf_g, P.lnf_b, P.fn_g, P.fn_b, 1);
+            ln_rows_to_smem<true>(P, sub, sm.a_rm, P.x, P.lnf_g, P.lnf_b, P.fn_g, P.fn_b, 1);
           }
           break;
         }

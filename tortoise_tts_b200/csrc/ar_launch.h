@@ -27,5 +27,9 @@ void launch_reset_sampler(int n_seqs, int seen_words, uint32_t* seen, int* finis
                           int* n_active, int start_mel, int* attn_cnt, int n_cnt, cudaStream_t st);
 cudaError_t launch_program(const Params& P, int smem_bytes, cudaStream_t st);
 int program_max_ctas_per_sm(int smem_bytes);
+// head-cluster decode kernel (ar_decode.cu)
+void launch_pack_projk(const void* src, int dtype, uint4* dst, cudaStream_t st);
+cudaError_t launch_decode(const Params& P, int smem_bytes, cudaStream_t st);
+int decode_max_clusters(int smem_bytes);
 
 }  // namespace tts

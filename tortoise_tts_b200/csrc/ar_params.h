@@ -25,7 +25,9 @@ enum InstrFlags : int {
   F_BARRIER_BEFORE = 1,  // grid barrier before executing
   F_CHECK_EXIT = 2,      // after the barrier: leave the launch if no sequence is unfinished
   F_ROW_MAP = 4,         // OP_HEAD / OP_LATENT: read x rows through head_rows[]
-  F_PLAN = 8             // OP_LN_QKV of layer 0 in decode: last CTA also builds the attention split plan
+  F_PLAN = 8,            // OP_LN_QKV of layer 0 in decode: last CTA also builds the attention split plan
+  F_FIXED_SRC = 32,      // LayerNorm source is the fixed-point accumulator P.y
+  F_ROW_RANGE = 16       // epilogue writes rows [pad0, pad1) only (cluster decode kernel: the other half is the sibling's)
 };
 
 struct Instr {
@@ -40,6 +42,7 @@ struct Instr {
 
 struct LayerDev {
   const uint4 *w_qkv, *w_proj, *w_fc, *w_proj2;            // packed chunks (layout.h)
+  const uint4* w_projk;                                    // attn.c_proj again, split-K chunks (layout.h projk_elem_offset)
   const float *ln1_g, *ln1_b, *ln2_g, *ln2_b;
   const float *b_qkv, *b_proj, *b_fc, *b_proj2;
 };
@@ -61,6 +64,9 @@ struct Params {
   const float *mel_emb, *mel_pos;
   // activations (row-indexed)
   float* x;              // [rows][1024] residual stream, fp32
+  long long* y;          // cluster decode kernel: [16][1024] residual stream between the attention and MLP blocks,
+                         //   accumulated by the 16 heads with integer atomics in 2^-32 fixed point (order-independent
+                         //   => deterministic); zero outside phases A..C of a layer; nullptr in the interpreter kernel
   float* q;              // [rows][1024] query, pre-scaled by 1/sqrt(64)
   __nv_bfloat16* ctx;    // A-fragment layout, K = 1024
   __nv_bfloat16* hbuf;   // A-fragment layout, K = 4096

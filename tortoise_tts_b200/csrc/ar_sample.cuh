@@ -21,7 +21,7 @@ __device__ __forceinline__ uint32_t key_of(float v) { return float_key(__float_a
 // count mode: pred(T) = #{key >= T} ... (see callers).  Implemented inline at the call sites.
 
 // One sequence.  `sc` = V floats (scores), `ev` = V floats scratch, both shared.  All 512 consumer threads call.
-__device__ void sample_row(const Params& P, const Smem& sm, int seq, int step_col) {
+static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int step_col) {
   Ctrl* c = sm.ctrl;
   float* sc = reinterpret_cast<float*>(sm.a_rm);
   float* ev = sm.red;
@@ -198,7 +198,7 @@ __device__ void sample_row(const Params& P, const Smem& sm, int seq, int step_co
   consumer_sync();   // sc / ev / scratch are reused by the next row
 }
 
-__device__ void sample_stage(const Params& P, const Instr& ins, const Smem& sm, int step_col) {
+static __device__ void sample_stage(const Params& P, const Instr& ins, const Smem& sm, int step_col) {
   for (int seq = blockIdx.x; seq < P.n_seqs; seq += P.G) sample_row(P, sm, seq, step_col);
 }
 

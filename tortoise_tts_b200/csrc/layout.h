@@ -83,6 +83,30 @@ TTS_HD void tile_range(int n_tiles, int G, int rot, int cta, int* t0, int* cnt) 
 }
 TTS_HD int next_rot(int n_tiles, int G, int rot) { return (rot + n_tiles % G) % G; }
 
+// ---- head-cluster decode kernel (ar_decode.cu) ---------------------------------------------------------
+// 32 clusters x 4 CTAs (B200 co-schedules 33 clusters of 4 but only 15 of 8): cluster c owns attention head
+// h = c >> 1 for the 8 rows [8*(c&1), 8*(c&1)+8).  CTA rank r computes 16 q/k/v columns of the head
+// (n8-tiles h*8 + 2r, 2r+1 of the q, k and v thirds of c_attn -- the sibling cluster streams the same weights,
+// normally an L2 hit), the attention of rows 8*(c&1) + 2r, +1, and output columns [256r, 256r+256) of the
+// split-K attn.c_proj product  ctx[rows, 64h..64h+64) . W[64h..64h+64, :].
+constexpr int kClusterSize = 4;
+constexpr int kDecClusters = 2 * kH;
+constexpr int kDecCtas = kClusterSize * kDecClusters;   // 128
+constexpr int kDecRows = 16;                            // rows (sequences) the cluster kernel handles
+constexpr int kProjkChunks = kH * 8;                    // split-K chunks per layer: (head, 128-column block)
+// attn.c_proj split-K chunk (16 KiB) of (head h, column block cb): W[64h + k][128cb + n], k < 64, n < 128, stored
+//   chunk[tile (16)][s (2)][lane (32)] = uint4 { b0(kb=2s), b1(kb=2s), b0(kb=2s+1), b1(kb=2s+1) }
+// with b0/b1 as in chunk_elem_offset.  Returns the bf16 element offset inside the chunk.
+TTS_HD int projk_elem_offset(int k, int n) {
+  int tile = n >> 3, g = n & 7;
+  int kb = k >> 4, kk = k & 15;
+  int s = kb >> 1, odd = kb & 1;
+  int t = (kk & 7) >> 1, half = kk & 1, hi = kk >> 3;
+  int lane = g * 4 + t;
+  int word = odd * 2 + hi;
+  return (((tile * 2 + s) * 32 + lane) * 4 + word) * 2 + half;
+}
+
 // monotone float -> uint key (larger float <=> larger key); -inf maps below every finite value.
 TTS_HD uint32_t float_key(uint32_t bits) { return (bits & 0x80000000u) ? ~bits : (bits | 0x80000000u); }
 

@@ -73,7 +73,7 @@ static int create_impl(TtsArHandle* h) {
 
   const size_t L = (size_t)c.n_layers;
   // packed weight arena: per layer 384 + 128 + 512 + 512 chunks; head v_tiles chunks
-  const size_t chunks_per_layer = kD3 / 8 + kD / 8 + kD4 / 8 + (kD / 8) * 4;
+  const size_t chunks_per_layer = kD3 / 8 + kD / 8 + kD4 / 8 + (kD / 8) * 4 + kProjkChunks;
   const size_t u4_per_chunk = kChunkBytes / 16;
   DALLOC(h, h->d_warena, (L * chunks_per_layer + h->v_tiles) * u4_per_chunk);
   h->d_w_head = h->d_warena + L * chunks_per_layer * u4_per_chunk;
@@ -89,6 +89,7 @@ static int create_impl(TtsArHandle* h) {
     ld.w_proj = wb + (size_t)(kD3 / 8) * u4_per_chunk;
     ld.w_fc = ld.w_proj + (size_t)(kD / 8) * u4_per_chunk;
     ld.w_proj2 = ld.w_fc + (size_t)(kD4 / 8) * u4_per_chunk;
+    ld.w_projk = ld.w_proj2 + (size_t)(kD / 8) * 4 * u4_per_chunk;
     float* fb = h->d_fparams + i * fp_per_layer;
     ld.ln1_g = fb; ld.ln1_b = fb + kD; ld.ln2_g = fb + 2 * kD; ld.ln2_b = fb + 3 * kD;
     ld.b_qkv = fb + 4 * kD; ld.b_proj = fb + 4 * kD + kD3; ld.b_fc = ld.b_proj + kD; ld.b_proj2 = ld.b_fc + kD4;
@@ -104,6 +105,7 @@ static int create_impl(TtsArHandle* h) {
 
   DALLOC(h, h->d_x, (size_t)h->rows_cap * kD);
   DALLOC(h, h->d_q, (size_t)h->rows_cap * kD);
+  DALLOC(h, h->d_y, (size_t)kDecRows * kD);
   DALLOC(h, h->d_ctx, (size_t)h->rows_cap * kD);
   DALLOC(h, h->d_h, (size_t)h->rows_cap * kD4);
   DALLOC(h, h->d_logits, (size_t)h->logit_rows_cap * h->v_stride);
@@ -151,6 +153,14 @@ static int create_impl(TtsArHandle* h) {
   TTS_CUDA(h, cudaEventCreate(&h->ev2));
   const int smem1 = smem_total_bytes(1, smem_max_slots(1, h->smem_budget));
   if (program_max_ctas_per_sm(smem1) < 1) return fail(h, TTS_AR_ERR_DEVICE, "interpreter kernel does not fit on an SM");
+  {
+    const char* e = getenv("TTS_AR_DECODE");   // "interp": force the interpreter kernel for decode (bring-up / A-B runs)
+    const int smemd = smem_total_bytes(1, smem_max_slots(1, h->smem_budget));
+    const int ncl = decode_max_clusters(smemd);
+    h->use_cluster = !(e && std::string(e) == "interp") && ncl >= kDecClusters;
+    if (getenv("TTS_AR_VERBOSE")) fprintf(stderr, "[tts_ar] co-resident clusters of %d CTAs: %d (smem %d B) -> decode kernel: %s\n",
+                                          kClusterSize, ncl, smemd, h->use_cluster ? "head-cluster" : "interpreter");
+  }
   TTS_CUDA(h, cudaDeviceSynchronize());
   return 0;
 }
@@ -211,6 +221,7 @@ extern "C" int tts_ar_load_weights(TtsArHandle* h, const TtsArWeights* w, void* 
     launch_pack_weight(lw.attn_proj_w, dt, const_cast<uint4*>(ld.w_proj), kD, kD, kD / 8, 0, st);
     launch_pack_weight(lw.c_fc_w, dt, const_cast<uint4*>(ld.w_fc), kD, kD4, kD4 / 8, 0, st);
     launch_pack_weight(lw.mlp_proj_w, dt, const_cast<uint4*>(ld.w_proj2), kD4, kD, kD / 8, 0, st);
+    launch_pack_projk(lw.attn_proj_w, dt, const_cast<uint4*>(ld.w_projk), st);
     launch_to_f32(lw.ln_1_w, dt, const_cast<float*>(ld.ln1_g), kD, kD, st);
     launch_to_f32(lw.ln_1_b, dt, const_cast<float*>(ld.ln1_b), kD, kD, st);
     launch_to_f32(lw.ln_2_w, dt, const_cast<float*>(ld.ln2_g), kD, kD, st);
@@ -219,7 +230,7 @@ extern "C" int tts_ar_load_weights(TtsArHandle* h, const TtsArWeights* w, void* 
     launch_to_f32(lw.attn_proj_b, dt, const_cast<float*>(ld.b_proj), kD, kD, st);
     launch_to_f32(lw.c_fc_b, dt, const_cast<float*>(ld.b_fc), kD4, kD4, st);
     launch_to_f32(lw.mlp_proj_b, dt, const_cast<float*>(ld.b_proj2), kD, kD, st);
-    h->launches += 12;
+    h->launches += 13;
   }
   const void* tops[] = {w->ln_f_w, w->ln_f_b, w->final_norm_w, w->final_norm_b, w->mel_head_w, w->mel_head_b,
                         w->mel_embedding, w->mel_pos_embedding, w->text_embedding, w->text_pos_embedding};

@@ -35,6 +35,8 @@ struct TtsArHandle {
   float *d_mel_emb = nullptr, *d_mel_pos = nullptr, *d_text_emb = nullptr, *d_text_pos = nullptr;
 
   // activations / cache (device)
+  long long* d_y = nullptr;            // cluster decode kernel: attention-block accumulator [16][1024]
+  bool use_cluster = false;         // 16 clusters of 8 CTAs can be co-resident (checked at create)
   float *d_x = nullptr, *d_q = nullptr, *d_logits = nullptr, *d_cur_latent = nullptr, *d_part = nullptr;
   __nv_bfloat16 *d_ctx = nullptr, *d_h = nullptr, *d_kv = nullptr;
   int *d_prefix_pt = nullptr, *d_priv_pt = nullptr, *d_utt_plen = nullptr;

@@ -46,11 +46,23 @@ int build_decode_program(TtsArHandle* h, cudaStream_t st) {
   return 0;
 }
 
-static int launch(TtsArHandle* h, Params& P, cudaStream_t st) {
+static int launch(TtsArHandle* h, Params& P, cudaStream_t st, bool cluster = false) {
   P.n_slots = smem_max_slots(P.mt_max, h->smem_budget);
   if (P.n_slots < 2) return fail(h, TTS_AR_ERR_DEVICE, "not enough shared memory for the weight ring");
   TTS_CUDA(h, cudaMemsetAsync(h->d_bar, 0, sizeof(unsigned int), st));
-  cudaError_t e = launch_program(P, smem_total_bytes(P.mt_max, P.n_slots), st);
+  cudaError_t e;
+  if (cluster) {
+    P.G = kDecCtas;
+    P.y = h->d_y;
+    P.mt_max = 1;
+    P.n_slots = smem_max_slots(1, h->smem_budget);
+    TTS_CUDA(h, cudaMemsetAsync(h->d_y, 0, sizeof(long long) * kDecRows * kD, st));
+    e = launch_decode(P, smem_total_bytes(1, P.n_slots), st);
+    if (e != cudaSuccess) return cuda_fail(h, e, "cudaLaunchKernelEx(ar_decode_kernel)");
+    h->launches += 1;
+    return 0;
+  }
+  e = launch_program(P, smem_total_bytes(P.mt_max, P.n_slots), st);
   if (e != cudaSuccess) return cuda_fail(h, e, "cudaLaunchCooperativeKernel(ar_program_kernel)");
   h->launches += 1;
   return 0;
@@ -190,7 +202,7 @@ static int run_steps(TtsArHandle* h, const TtsArSampling* s, int n_steps, bool s
   P.temperature = s->temperature; P.top_p = s->top_p; P.rep_penalty = s->repetition_penalty;
   P.seed = s->seed; P.seq_index_base = s->seq_index_base;
   P.out_codes = out_codes; P.out_stride = n_steps; P.out_latents = out_latents; P.forced = forced; P.out_choice = out_choice;
-  int rc = launch(h, P, st);
+  int rc = launch(h, P, st, h->use_cluster && h->n_seqs <= kDecRows);
   if (rc) return rc;
   // SURVEY.md 8(d) algorithmic bytes, assuming every sequence stays live (exact under ignore_eos)
   const double W = 2.0 * ((double)c.n_layers * 12596224.0 + 4096.0 + (double)c.n_mel_codes * (kD + 1));
