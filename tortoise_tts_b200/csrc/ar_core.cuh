@@ -293,25 +293,22 @@ template <bool kDouble>
 __device__ void ln_rows_to_smem(const Params& P, const Instr& ins, uint8_t* a_rm, const float* src, const float* g1, const float* b1,
                                 const float* g2, const float* b2, int mt_count) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#ifdef TTS_LN_PREFETCH
   prefetch_l1(g1 + 32 * lane);
   prefetch_l1(b1 + 32 * lane);
   if (kDouble) {
     prefetch_l1(g2 + 32 * lane);
     prefetch_l1(b2 + 32 * lane);
   }
+#endif
   for (int r0 = w; r0 < mt_count * 16; r0 += 2 * kNW) {
     const int r1 = r0 + kNW;
     const bool ok0 = r0 < ins.nrows, ok1 = r1 < ins.nrows;
+    // rows past the end are computed on a clamped (valid) row and stored as zeros: no divergent load paths
+    const int l0 = ins.row0 + (ok0 ? r0 : 0), l1 = ins.row0 + (ok1 ? r1 : 0);   // logical rows (logits / latent rows)
     float4 v0[8], v1[8];
-    int l0 = 0, l1 = 0;
-    if (ok0) {
-      l0 = ins.row0 + r0;                                   // logical row (logits / latent row)
-      ln_load_row(P, ins, src, (ins.flags & F_ROW_MAP) ? P.head_rows[l0] : l0, lane, v0);
-    }
-    if (ok1) {
-      l1 = ins.row0 + r1;
-      ln_load_row(P, ins, src, (ins.flags & F_ROW_MAP) ? P.head_rows[l1] : l1, lane, v1);
-    }
+    ln_load_row(P, ins, src, (ins.flags & F_ROW_MAP) ? P.head_rows[l0] : l0, lane, v0);
+    ln_load_row(P, ins, src, (ins.flags & F_ROW_MAP) ? P.head_rows[l1] : l1, lane, v1);
     uint8_t* d0 = a_rm + (size_t)r0 * kARowBytes;
     uint8_t* d1 = a_rm + (size_t)r1 * kARowBytes;
     if (ok0) {

@@ -85,20 +85,222 @@ __device__ void dec_producer(const Params& P, Ctrl* c, uint8_t* ring, int head, 
   }
 }
 
-// ---- attention of head `head` for rows rbase, rbase+1: 4 position ranges per row, merged in shared memory ----
+// ---- per-step row facts of this CTA, kept in shared memory (upper part of the reduction buffer) ----------------
+// Positions and page tables do not change inside a step, so the dependent global loads
+// (row_pos -> utterance -> prompt length -> page table -> page) are done once per step, not once per layer.
+//   [0..15] page of every row's new position (-1: inactive row)   [16..31] its slot in the page
+//   [32+j] kv length of attention row j (j < 2, 0: inactive)      [34+j] prompt length of its utterance
+//   [64 + 64j + i] prefix page table (i < 32) / private page table (i >= 32) of attention row j
+constexpr int kRinfoOffsetFloats = 6144;
+__device__ __forceinline__ int* rinfo_ptr(const Smem& sm) { return reinterpret_cast<int*>(sm.red + kRinfoOffsetFloats); }
+
+__device__ void build_rinfo(const Params& P, int rbase, const Smem& sm) {
+  int* ri = rinfo_ptr(sm);
+  const int tid = threadIdx.x;
+  if (tid < 16) {
+    const int row = tid;
+    const int pos = (row < P.n_rows) ? ld_cg_i(P.row_pos + row) : -1;
+    int page = -1, slot = 0;
+    if (pos >= 0) {
+      const int pp = pos - P.utt_plen[P.row_utt[row]];          // decode rows are past their prompt
+      page = P.priv_pt[row * kMaxPagesPerSeg + (pp >> 5)];
+      slot = pp & 31;
+    }
+    ri[row] = page;
+    ri[16 + row] = slot;
+  } else if (tid >= 32 && tid < 34) {
+    const int j = tid - 32, row = rbase + j;
+    const int pos = (row < P.n_rows) ? ld_cg_i(P.row_pos + row) : -1;
+    ri[32 + j] = pos + 1;
+    ri[34 + j] = (row < P.n_rows) ? P.utt_plen[P.row_utt[row]] : 0;
+  } else if (tid >= 64 && tid < 192) {
+    const int j = (tid - 64) >> 6, i = (tid - 64) & 63, row = rbase + j;
+    int v = 0;
+    if (row < P.n_rows) v = (i < 32) ? P.prefix_pt[P.row_utt[row] * kMaxPagesPerSeg + i] : P.priv_pt[row * kMaxPagesPerSeg + (i - 32)];
+    ri[64 + 64 * j + i] = v;
+  }
+  consumer_sync();
+}
+
+// ---- cluster-cooperative LayerNorm: CTA rank r normalises rows 4r..4r+3 (warps 0..3, one row each) and writes
+// the bf16 rows into the A-operand buffer of all 4 CTAs of the cluster through distributed shared memory, so the
+// 16 rows are read from L2 once per cluster instead of once per CTA.  Warps 4..7 meanwhile pull the NEXT layer's
+// K/V pages of this CTA's attention rows into L2 (bulk prefetch), so the attention phase is not an HBM stall.
+// The caller follows with cluster_barrier().
+template <bool kDouble>
+__device__ void ln_cluster(const Params& P, const Instr& ins, const Smem& sm, const float* src, const float* g1, const float* b1,
+                           const float* g2, const float* b2, int rank, int head, int pf_layer) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (w < 4) {
+    const int r = 4 * rank + w;
+    const bool ok = r < ins.nrows;
+    const int lrow = ins.row0 + (ok ? r : 0);
+    float4 v[8];
+    ln_load_row(P, ins, src, lrow, lane, v);
+    prof_mark(P, sm.ctrl, 21);
+    ln_normalise(v, g1, b1, lane);
+    prof_mark(P, sm.ctrl, 22);
+    if (kDouble) {
+      ln_normalise(v, g2, b2, lane);
+      if (ins.op == OP_HEAD && blockIdx.x < kClusterSize && ok) {
+        float* lp = P.cur_latent + (size_t)lrow * kD;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) *reinterpret_cast<float4*>(lp + 128 * j + 4 * lane) = v[j];
+      }
+    }
+    uint8_t* dst = sm.a_rm + (size_t)r * kARowBytes;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const uint2 pk = ok ? make_uint2(pack_bf16x2(v[j].x, v[j].y), pack_bf16x2(v[j].z, v[j].w)) : make_uint2(0u, 0u);
+#pragma unroll
+      for (int d = 0; d < kClusterSize; ++d) st_cluster_u2(dst + (128 * j + 4 * lane) * 2, d, pk);
+    }
+    prof_mark(P, sm.ctrl, 23);
+  } else if (pf_layer >= 0 && pf_layer <= P.n_layers) {
+    const int t = threadIdx.x - 128;                 // 0..127
+    // the small fp32 parameters (LN gains/biases, GEMM biases: one contiguous block per layer, tts_ar.cu) are
+    // read once per step and do not survive 1.3 GB of streaming in L2: pull the next block in, 1/128 per CTA
+    if (t == 0) {
+      if (pf_layer < P.n_layers) {
+        constexpr int kPer = ((4 * kD + kD3 + kD + kD4 + kD) * 4 / kDecCtas + 15) / 16 * 16;   // 416 B
+        bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(P.layers[pf_layer].ln1_g) + (size_t)blockIdx.x * kPer, kPer);
+      } else {
+        const int per = ((4 * kD + P.v_stride) * 4 / kDecCtas + 15) / 16 * 16;
+        bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(P.lnf_g) + (size_t)blockIdx.x * per, per);
+      }
+    }
+    if (pf_layer == P.n_layers) return;
+    const int* ri = rinfo_ptr(sm);
+    const int j = t >> 6, i = t & 63, pg = i >> 1, kv = i & 1;
+    const int len = ri[32 + j], plen = ri[34 + j];
+    if (len > 0) {
+      const int* pt = ri + 64 + 64 * j;
+      const __nv_bfloat16* base = P.kv + kv_row_offset(pf_layer, P.n_pages, 0, kv, head, 0);
+      const size_t page_stride = (size_t)2 * kH * kPage * kHD;
+      if (pg * kPage < plen) bulk_prefetch_l2(base + (size_t)pt[pg] * page_stride, kPage * kHD * 2);
+      if (pg * kPage < len - plen) bulk_prefetch_l2(base + (size_t)pt[32 + pg] * page_stride, kPage * kHD * 2);
+    }
+  }
+}
+
+// ---- attention of head `head` for rows rbase, rbase+1 ------------------------------------------------------------
+// Warp w: row rbase + (w >> 2), quarter (w & 3) of the row's 16-position granules (a granule never straddles a
+// page).  K/V granules are double-buffered in registers so the next granule's 128-bit loads are in flight while
+// the current one is reduced; the four partial (max, sum, acc) states of a row are merged in shared memory.
+struct Gran {
+  uint4 k[4], v[4];
+  int cnt;
+};
+
+__device__ __forceinline__ void gran_load(Gran& G, const __nv_bfloat16* kvb, const int* pt, int g, int Gp, int plen, int len,
+                                          int rg) {
+  int pos0, cnt, page;
+  if (g < Gp) {
+    pos0 = 16 * g;
+    cnt = min(16, plen - pos0);
+    page = pt[pos0 >> 5];
+  } else {
+    pos0 = 16 * (g - Gp);
+    cnt = min(16, len - plen - pos0);
+    page = pt[32 + (pos0 >> 5)];
+  }
+  const __nv_bfloat16* kb = kvb + (size_t)page * (2 * kH * kPage * kHD) + (pos0 & 31) * kHD;
+  const __nv_bfloat16* vb = kb + (size_t)kH * kPage * kHD;
+  G.cnt = cnt;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int r = 4 * j + rg;
+    G.k[j] = (r < cnt) ? ld_cg_u4(kb + r * kHD) : make_uint4(0u, 0u, 0u, 0u);
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int r = 4 * j + rg;
+    G.v[j] = (r < cnt) ? ld_cg_u4(vb + r * kHD) : make_uint4(0u, 0u, 0u, 0u);
+  }
+}
+
+__device__ __forceinline__ void gran_reduce(const Gran& G, const float (&qv)[8], int rg, float& m, float& l, float (&acc)[8]) {
+  float sc[4];
+  float cm = -INFINITY;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    float s = qv[0] * bf16_lo(G.k[j].x);
+    s = fmaf(qv[1], bf16_hi(G.k[j].x), s);
+    s = fmaf(qv[2], bf16_lo(G.k[j].y), s);
+    s = fmaf(qv[3], bf16_hi(G.k[j].y), s);
+    s = fmaf(qv[4], bf16_lo(G.k[j].z), s);
+    s = fmaf(qv[5], bf16_hi(G.k[j].z), s);
+    s = fmaf(qv[6], bf16_lo(G.k[j].w), s);
+    s = fmaf(qv[7], bf16_hi(G.k[j].w), s);
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    sc[j] = (4 * j + rg < G.cnt) ? s : -INFINITY;
+    cm = fmaxf(cm, sc[j]);
+  }
+  cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, 8));
+  cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, 16));
+  const float m_new = fmaxf(m, cm);                 // finite: cnt >= 1
+  const float scale = exp2f(m - m_new);             // m == -inf -> 0
+  l *= scale;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] *= scale;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float pj = exp2f(sc[j] - m_new);          // masked rows: exp2(-inf) = 0
+    l += pj;
+    acc[0] = fmaf(pj, bf16_lo(G.v[j].x), acc[0]);
+    acc[1] = fmaf(pj, bf16_hi(G.v[j].x), acc[1]);
+    acc[2] = fmaf(pj, bf16_lo(G.v[j].y), acc[2]);
+    acc[3] = fmaf(pj, bf16_hi(G.v[j].y), acc[3]);
+    acc[4] = fmaf(pj, bf16_lo(G.v[j].z), acc[4]);
+    acc[5] = fmaf(pj, bf16_hi(G.v[j].z), acc[5]);
+    acc[6] = fmaf(pj, bf16_lo(G.v[j].w), acc[6]);
+    acc[7] = fmaf(pj, bf16_hi(G.v[j].w), acc[7]);
+  }
+  m = m_new;
+}
+
 __device__ void attn_local(const Params& P, int layer, int head, int rbase, const Smem& sm) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int rg = lane >> 3, dc = lane & 7;
+  const int* ri = rinfo_ptr(sm);
   float* part = sm.red;                               // [8 warps][kPartStride]
   {
-    const int row = rbase + (w >> 2), s = w & 3;
-    const int len = (row < P.n_rows) ? ld_cg_i(P.row_pos + row) + 1 : 0;
+    const int j = w >> 2, s = w & 3, row = rbase + j;
+    const int len = ri[32 + j], plen = ri[34 + j];
     float m = -INFINITY, l = 0.f, acc[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc[i] = 0.f;
     if (len > 0) {
-      const int p0 = (s * len) >> 2, p1 = ((s + 1) * len) >> 2;
-      if (p1 > p0) attn_unit(P, layer, row, head, p0, p1, m, l, acc);
+      const int Gp = (plen + 15) >> 4, Gt = Gp + ((len - plen + 15) >> 4);
+      const int g0 = (s * Gt) >> 2, g1 = ((s + 1) * Gt) >> 2;
+      if (g1 > g0) {
+        const int* pt = ri + 64 + 64 * j;
+        const __nv_bfloat16* kvb = P.kv + kv_row_offset(layer, P.n_pages, 0, 0, head, 0) + dc * 8;
+        Gran A, B;
+        gran_load(A, kvb, pt, g0, Gp, plen, len, rg);
+        float qv[8];
+        {
+          const float* qp = P.q + (size_t)row * kD + head * kHD + dc * 8;
+          const float4 a = ld_cg_f4(qp), b = ld_cg_f4(qp + 4);
+          qv[0] = a.x * kLog2e; qv[1] = a.y * kLog2e; qv[2] = a.z * kLog2e; qv[3] = a.w * kLog2e;
+          qv[4] = b.x * kLog2e; qv[5] = b.y * kLog2e; qv[6] = b.z * kLog2e; qv[7] = b.w * kLog2e;
+        }
+        for (int g = g0; g < g1; g += 2) {
+          if (g + 1 < g1) gran_load(B, kvb, pt, g + 1, Gp, plen, len, rg);
+          gran_reduce(A, qv, rg, m, l, acc);
+          if (g + 2 < g1) gran_load(A, kvb, pt, g + 2, Gp, plen, len, rg);
+          if (g + 1 < g1) gran_reduce(B, qv, rg, m, l, acc);
+        }
+        l += __shfl_xor_sync(0xffffffffu, l, 8);
+        l += __shfl_xor_sync(0xffffffffu, l, 16);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 8);
+          acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 16);
+        }
+      }
     }
     float* pp = part + w * kPartStride;
     if (rg == 0) {
@@ -110,29 +312,27 @@ __device__ void attn_local(const Params& P, int layer, int head, int rbase, cons
   consumer_sync();
   if (w < 2) {
     const int row = rbase + w;
-    if (row < kDecRows) {
-      const int len = (row < P.n_rows) ? ld_cg_i(P.row_pos + row) + 1 : 0;
-      float o0 = 0.f, o1 = 0.f;
-      if (len > 0) {
-        const float* pb = part + (4 * w) * kPartStride;
-        float M = -INFINITY;
+    const int len = ri[32 + w];
+    float o0 = 0.f, o1 = 0.f;
+    if (len > 0) {
+      const float* pb = part + (4 * w) * kPartStride;
+      float M = -INFINITY;
 #pragma unroll
-        for (int s = 0; s < 4; ++s) M = fmaxf(M, pb[s * kPartStride]);
-        float L = 0.f;
+      for (int s = 0; s < 4; ++s) M = fmaxf(M, pb[s * kPartStride]);
+      float L = 0.f;
 #pragma unroll
-        for (int s = 0; s < 4; ++s) {
-          const float wgt = exp2f(pb[s * kPartStride] - M);       // empty range: exp2(-inf) = 0
-          L = fmaf(wgt, pb[s * kPartStride + 1], L);
-          const float2 a = *reinterpret_cast<const float2*>(pb + s * kPartStride + 8 + 2 * lane);
-          o0 = fmaf(wgt, a.x, o0);
-          o1 = fmaf(wgt, a.y, o1);
-        }
-        const float inv = 1.0f / L;
-        o0 *= inv;
-        o1 *= inv;
+      for (int s = 0; s < 4; ++s) {
+        const float wgt = exp2f(pb[s * kPartStride] - M);       // empty range: exp2(-inf) = 0
+        L = fmaf(wgt, pb[s * kPartStride + 1], L);
+        const float2 a = *reinterpret_cast<const float2*>(pb + s * kPartStride + 8 + 2 * lane);
+        o0 = fmaf(wgt, a.x, o0);
+        o1 = fmaf(wgt, a.y, o1);
       }
-      write_ctx_pair(P, row, head * kHD + 2 * lane, o0, o1);
+      const float inv = 1.0f / L;
+      o0 *= inv;
+      o1 *= inv;
     }
+    write_ctx_pair(P, row, head * kHD + 2 * lane, o0, o1);
   }
 }
 
@@ -254,8 +454,16 @@ __global__ void __launch_bounds__(kThreads, 1) ar_decode_kernel(const __grid_con
       if (!alive) break;
       prof_mark(P, c, 200 + OP_LN_QKV);
       if (layer == 0 && ld_cg_i(P.n_active) == 0) { alive = false; break; }
-      ins.op = OP_LN_QKV; ins.flags = F_ROW_RANGE; ins.pad0 = row_lo; ins.pad1 = row_lo + 8;
-      gemm_tiles<1>(P, ins, sm, pipe, head * 8 + 2 * rank, 6, kD / 8, 2, P.x);
+      if (layer == 0) build_rinfo(P, row_lo + 2 * rank, sm);
+      ins.op = OP_LN_QKV; ins.flags = 0;
+      const bool ln_local = P.dbg_flags & 1;
+      if (!ln_local) {
+        ln_cluster<false>(P, ins, sm, P.x, P.layers[layer].ln1_g, P.layers[layer].ln1_b, nullptr, nullptr, rank, head, layer + 1);
+        if (!(alive = cluster_barrier(c, cphase))) break;
+        prof_mark(P, c, 1);
+      }
+      ins.flags = F_ROW_RANGE; ins.pad0 = row_lo; ins.pad1 = row_lo + 8;
+      gemm_tiles<1>(P, ins, sm, pipe, head * 8 + 2 * rank, 6, kD / 8, 2, P.x, !ln_local);
       ins.flags = 0;
       if (!(alive = cluster_barrier(c, cphase))) break;
       prof_mark(P, c, 200 + OP_ATTN);
@@ -269,7 +477,12 @@ __global__ void __launch_bounds__(kThreads, 1) ar_decode_kernel(const __grid_con
       if (!alive) break;
       prof_mark(P, c, 200 + OP_LN_FC);
       ins.op = OP_LN_FC; ins.flags = F_FIXED_SRC;
-      gemm_tiles<1>(P, ins, sm, pipe, blockIdx.x * 4, 4, 0, 1 << 30, P.x);
+      if (!ln_local) {
+        ln_cluster<false>(P, ins, sm, P.x, P.layers[layer].ln2_g, P.layers[layer].ln2_b, nullptr, nullptr, rank, head, -1);
+        if (!(alive = cluster_barrier(c, cphase))) break;
+        prof_mark(P, c, 1);
+      }
+      gemm_tiles<1>(P, ins, sm, pipe, blockIdx.x * 4, 4, 0, 1 << 30, P.x, !ln_local);
       // ---- phase C: mlp.c_proj, x = y + . ----
       prof_mark(P, c, 100 + OP_PROJ2);
       alive = grid_barrier(P, c, epoch);
@@ -284,8 +497,10 @@ __global__ void __launch_bounds__(kThreads, 1) ar_decode_kernel(const __grid_con
     alive = grid_barrier(P, c, epoch);
     if (!alive) break;
     prof_mark(P, c, 200 + OP_HEAD);
-    ins.op = OP_HEAD; ins.layer = 0;
-    gemm_tiles<1>(P, ins, sm, pipe, ht0, hcnt, 0, 1 << 30, P.x);
+    ins.op = OP_HEAD; ins.layer = 0; ins.flags = 0;
+    ln_cluster<true>(P, ins, sm, P.x, P.lnf_g, P.lnf_b, P.fn_g, P.fn_b, rank, head, 0);
+    if (!(alive = cluster_barrier(c, cphase))) break;
+    gemm_tiles<1>(P, ins, sm, pipe, ht0, hcnt, 0, 1 << 30, P.x, true);
     if (c->abort_flag) alive = false;
   }
   consumer_sync();

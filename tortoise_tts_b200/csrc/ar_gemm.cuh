@@ -79,7 +79,7 @@ __device__ __forceinline__ void gemm_epilogue(const Params& P, const Instr& ins,
 // of tile_range).
 template <int MT>
 __device__ void gemm_tiles(const Params& P, const Instr& ins, const Smem& sm, Pipe& pipe, int t0, int cnt, int tstride,
-                           int tinner, const float* ln_src) {
+                           int tinner, const float* ln_src, bool a_staged = false) {
   constexpr int KS = kNW / MT;             // k-slices
   constexpr int KPW = kKbPerChunk / KS;    // k16-blocks per warp per chunk (4 * MT)
   constexpr int KB = KPW > 16 ? 16 : KPW;  // A-fragment batch
@@ -94,7 +94,7 @@ __device__ void gemm_tiles(const Params& P, const Instr& ins, const Smem& sm, Pi
   const bool a_from_smem = (ins.op == OP_LN_QKV || ins.op == OP_LN_FC || ins.op == OP_HEAD);
 
   // ---- A operand ----
-  if (a_from_smem) {
+  if (a_from_smem && !a_staged) {
     if (ins.op == OP_LN_QKV)
       ln_rows_to_smem<false>(P, ins, sm.a_rm, ln_src, P.layers[ins.layer].ln1_g, P.layers[ins.layer].ln1_b, nullptr, nullptr, MT);
     else if (ins.op == OP_LN_FC)

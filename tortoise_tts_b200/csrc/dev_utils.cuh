@@ -117,6 +117,19 @@ __device__ __forceinline__ void mbar_arrive_remote(uint64_t* local_bar, uint32_t
       "r"(rank)
       : "memory");
 }
+// 8-byte store into the shared memory of CTA `rank` of this cluster, at the offset of `local_ptr`
+__device__ __forceinline__ void st_cluster_u2(void* local_ptr, uint32_t rank, uint2 v) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "st.shared::cluster.v2.u32 [ra], {%2, %3};\n\t}" ::"r"(smem_u32(local_ptr)),
+      "r"(rank), "r"(v.x), "r"(v.y)
+      : "memory");
+}
+// fire-and-forget bulk prefetch of `bytes` (multiple of 16) of global memory into L2
+__device__ __forceinline__ void bulk_prefetch_l2(const void* p, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(

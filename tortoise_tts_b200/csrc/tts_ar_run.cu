@@ -1,6 +1,7 @@
 // tts_ar_run.cu -- C ABI call path: prompt pass, sample loop, latent re-forward, host-buffer entry.
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <algorithm>
 #include "tts_ar_host.h"
 
@@ -56,6 +57,8 @@ static int launch(TtsArHandle* h, Params& P, cudaStream_t st, bool cluster = fal
     P.y = h->d_y;
     P.mt_max = 1;
     P.n_slots = smem_max_slots(1, h->smem_budget);
+    if (const char* e = getenv("TTS_AR_DBG")) P.dbg_flags = atoi(e);
+    if (const char* e = getenv("TTS_AR_SLOTS")) P.n_slots = std::max(2, std::min(P.n_slots, atoi(e)));   // bring-up: ring depth
     TTS_CUDA(h, cudaMemsetAsync(h->d_y, 0, sizeof(long long) * kDecRows * kD, st));
     e = launch_decode(P, smem_total_bytes(1, P.n_slots), st);
     if (e != cudaSuccess) return cuda_fail(h, e, "cudaLaunchKernelEx(ar_decode_kernel)");
