@@ -91,7 +91,7 @@ __device__ void dec_producer(const Params& P, Ctrl* c, uint8_t* ring, int head, 
 //   [0..15] page of every row's new position (-1: inactive row)   [16..31] its slot in the page
 //   [32+j] kv length of attention row j (j < 2, 0: inactive)      [34+j] prompt length of its utterance
 //   [64 + 64j + i] prefix page table (i < 32) / private page table (i >= 32) of attention row j
-constexpr int kRinfoOffsetFloats = 6144;
+constexpr int kRinfoOffsetFloats = 7168;     // above the 24 KiB the 6-tile split-K reduction uses
 __device__ __forceinline__ int* rinfo_ptr(const Smem& sm) { return reinterpret_cast<int*>(sm.red + kRinfoOffsetFloats); }
 
 __device__ void build_rinfo(const Params& P, int rbase, const Smem& sm) {
@@ -336,6 +336,90 @@ __device__ void attn_local(const Params& P, int layer, int head, int rbase, cons
   }
 }
 
+// ---- 16-row GEMM over this CTA's next `cnt` (<= NT) streamed K=1024 chunks ------------------------------------------
+// A = the LayerNorm'd rows staged in sm.a_rm; warp w owns k16-blocks 8w..8w+7 of every chunk (its A fragments
+// are loaded once), the 8 partial tiles are summed through shared memory in a fixed order (deterministic).
+// HALF: only rows [row_lo, row_lo + 8) are produced (c_attn: the other half belongs to the sibling cluster).
+// epi(row, col, v0, v1) receives the fp32 sums of columns col, col+1 (col = 8 * tile_of(i) + even offset).
+template <int NT, bool HALF, typename TileFn, typename Epi>
+__device__ __forceinline__ void gemm16(const Smem& sm, Pipe& pipe, int cnt, int row_lo, TileFn tile_of, Epi epi) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  Ctrl* c = sm.ctrl;
+  uint4 a[8];
+  {
+    const uint32_t base = smem_u32(sm.a_rm) + (uint32_t)(((lane & 7) + ((lane >> 3) & 1) * 8) * kARowBytes) +
+                          (uint32_t)((lane >> 4) * 16) + (uint32_t)(w * 8 * 32);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) ldmatrix_x4(base + (uint32_t)(i * 32), a[i].x, a[i].y, a[i].z, a[i].w);
+  }
+  float acc[NT][2][4];
+#pragma unroll
+  for (int t = 0; t < NT; ++t)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[t][0][j] = acc[t][1][j] = 0.f;
+  // all chunks of the pass have normally landed long ago: probe them back to back, block only if one has not
+  Pipe p2 = pipe;
+  bool ok = true;
+#pragma unroll
+  for (int t = 0; t < NT; ++t)
+    if (t < cnt) {
+      ok &= mbar_try_wait(&c->full[p2.slot], p2.phase);
+      p2.advance();
+    }
+  if (!ok) {
+    p2 = pipe;
+    for (int t = 0; t < cnt; ++t) {
+      mbar_wait(&c->full[p2.slot], p2.phase, &c->abort_flag);
+      p2.advance();
+    }
+  }
+  p2 = pipe;
+#pragma unroll
+  for (int t = 0; t < NT; ++t)
+    if (t < cnt) {
+      const uint4* bsm = reinterpret_cast<const uint4*>(sm.ring + (size_t)p2.slot * kChunkBytes) + (w * 4) * 32 + lane;
+#pragma unroll
+      for (int s2 = 0; s2 < 4; ++s2) {
+        const uint4 b = bsm[s2 * 32];
+        mma_bf16_16816(acc[t][s2 & 1], a[2 * s2], b.x, b.y);
+        mma_bf16_16816(acc[t][s2 & 1], a[2 * s2 + 1], b.z, b.w);
+      }
+      p2.advance();
+    }
+  __syncwarp();
+  if (lane == 0) {
+    Pipe p3 = pipe;
+    for (int t = 0; t < cnt; ++t) {
+      mbar_arrive(&c->empty[p3.slot]);
+      p3.advance();
+    }
+  }
+  pipe = p2;
+  float4* red4 = reinterpret_cast<float4*>(sm.red);
+#pragma unroll
+  for (int t = 0; t < NT; ++t)
+    if (t < cnt)
+      red4[(w * NT + t) * 32 + lane] = make_float4(acc[t][0][0] + acc[t][1][0], acc[t][0][1] + acc[t][1][1],
+                                                   acc[t][0][2] + acc[t][1][2], acc[t][0][3] + acc[t][1][3]);
+  consumer_sync();
+  const float2* red2 = reinterpret_cast<const float2*>(sm.red);
+  const int per_tile = HALF ? 32 : 64;
+  for (int e = threadIdx.x; e < cnt * per_tile; e += kConsumerThreads) {
+    const int t = e / per_tile, rem = e - t * per_tile;
+    const int ln = HALF ? rem : (rem >> 1);
+    const int hh = HALF ? (row_lo >> 3) : (rem & 1);
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int k = 0; k < kNW; ++k) {
+      const float2 v = red2[((k * NT + t) * 32 + ln) * 2 + hh];
+      s0 += v.x;
+      s1 += v.y;
+    }
+    epi((ln >> 2) + 8 * hh, tile_of(t) * 8 + 2 * (ln & 3), s0, s1);
+  }
+  consumer_sync();
+}
+
 // ---- split-K attn.c_proj: y[rows, 256r .. 256r+256) += ctx[rows, 64h .. 64h+64) . W[64h .. 64h+64, 256r ..] ------
 // rows = [row_lo, row_lo + 8): the half of the 16-row M tile this cluster owns (the other half of the A fragments
 // is the sibling cluster's and is ignored).  Two 16 KiB chunks of 128 columns; warp w: n8-tiles 2w, 2w+1 of each.
@@ -462,9 +546,30 @@ __global__ void __launch_bounds__(kThreads, 1) ar_decode_kernel(const __grid_con
         if (!(alive = cluster_barrier(c, cphase))) break;
         prof_mark(P, c, 1);
       }
-      ins.flags = F_ROW_RANGE; ins.pad0 = row_lo; ins.pad1 = row_lo + 8;
-      gemm_tiles<1>(P, ins, sm, pipe, head * 8 + 2 * rank, 6, kD / 8, 2, P.x, !ln_local);
-      ins.flags = 0;
+      if (ln_local) {
+        ins.flags = F_ROW_RANGE; ins.pad0 = row_lo; ins.pad1 = row_lo + 8;
+        gemm_tiles<1>(P, ins, sm, pipe, head * 8 + 2 * rank, 6, kD / 8, 2, P.x, false);
+        ins.flags = 0;
+      } else {
+        const float* bias = P.layers[layer].b_qkv;
+        const int* ri = rinfo_ptr(sm);
+        const int t0 = head * 8 + 2 * rank;
+        gemm16<6, true>(sm, pipe, 6, row_lo, [&](int i) { return t0 + (i >> 1) * (kD / 8) + (i & 1); },
+                        [&](int row, int col, float v0, float v1) {
+                          if (row >= n) return;
+                          v0 += bias[col];
+                          v1 += bias[col + 1];
+                          const int part = col >> 10, cc = col & (kD - 1);
+                          if (part == 0) {   // query, pre-scaled by 1/sqrt(64) (exact: power of two)
+                            *reinterpret_cast<float2*>(P.q + (size_t)row * kD + cc) = make_float2(v0 * 0.125f, v1 * 0.125f);
+                          } else {           // key / value -> page slot of this row's new position (row facts of the step)
+                            const int page = ri[row];
+                            if (page < 0) return;
+                            __nv_bfloat16* dst = P.kv + kv_row_offset(layer, P.n_pages, page, part - 1, cc >> 6, ri[16 + row]) + (cc & 63);
+                            *reinterpret_cast<uint32_t*>(dst) = pack_bf16x2(v0, v1);
+                          }
+                        });
+      }
       if (!(alive = cluster_barrier(c, cphase))) break;
       prof_mark(P, c, 200 + OP_ATTN);
       attn_local(P, layer, head, row_lo + 2 * rank, sm);
@@ -482,7 +587,17 @@ __global__ void __launch_bounds__(kThreads, 1) ar_decode_kernel(const __grid_con
         if (!(alive = cluster_barrier(c, cphase))) break;
         prof_mark(P, c, 1);
       }
-      gemm_tiles<1>(P, ins, sm, pipe, blockIdx.x * 4, 4, 0, 1 << 30, P.x, !ln_local);
+      if (ln_local) {
+        gemm_tiles<1>(P, ins, sm, pipe, blockIdx.x * 4, 4, 0, 1 << 30, P.x, false);
+      } else {
+        const float* bias = P.layers[layer].b_fc;
+        const int t0 = blockIdx.x * 4;
+        gemm16<4, false>(sm, pipe, 4, 0, [&](int i) { return t0 + i; }, [&](int row, int col, float v0, float v1) {
+          if (row >= n) return;
+          const float h0 = gelu_new(v0 + bias[col]), h1 = gelu_new(v1 + bias[col + 1]);
+          *reinterpret_cast<uint32_t*>(P.hbuf + afrag_elem_offset(row, col, kD4)) = pack_bf16x2(h0, h1);
+        });
+      }
       // ---- phase C: mlp.c_proj, x = y + . ----
       prof_mark(P, c, 100 + OP_PROJ2);
       alive = grid_barrier(P, c, epoch);
@@ -500,7 +615,15 @@ __global__ void __launch_bounds__(kThreads, 1) ar_decode_kernel(const __grid_con
     ins.op = OP_HEAD; ins.layer = 0; ins.flags = 0;
     ln_cluster<true>(P, ins, sm, P.x, P.lnf_g, P.lnf_b, P.fn_g, P.fn_b, rank, head, 0);
     if (!(alive = cluster_barrier(c, cphase))) break;
-    gemm_tiles<1>(P, ins, sm, pipe, ht0, hcnt, 0, 1 << 30, P.x, true);
+    for (int tb = 0; tb < hcnt; tb += 6) {
+      const int t0 = ht0 + tb;
+      gemm16<6, false>(sm, pipe, min(6, hcnt - tb), 0, [&](int i) { return t0 + i; }, [&](int row, int col, float v0, float v1) {
+        if (row >= n) return;
+        float* lp = P.logits + (size_t)row * P.v_stride + col;
+        if (col < P.V) lp[0] = v0 + P.b_head[col];
+        if (col + 1 < P.V) lp[1] = v1 + P.b_head[col + 1];
+      });
+    }
     if (c->abort_flag) alive = false;
   }
   consumer_sync();
