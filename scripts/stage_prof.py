@@ -34,15 +34,28 @@ if "TTS_AR_PROF_STEP" in os.environ:
     t = raw[: 2 * n_instr].reshape(n_instr, 2)
     marks = raw[1024:].reshape(-1, 2)
     marks = marks[marks[:, 1] > 0]
-    names = {1: "A-ready", 2: "mma-done", 3: "epi-done", 11: "attn-plan", 21: "ln-loaded", 22: "ln-normalised", 23: "ln-dsmem-stored"}
+    names = {1: "A-ready", 2: "mma-done", 3: "epi-done", 11: "attn-plan", 21: "ln-loaded", 22: "ln-normalised", 23: "ln-dsmem-stored", 31: "smp-scores+max", 32: "smp-exp+Z", 33: "smp-top-p", 34: "smp-multinomial", 35: "smp-bookkeeping"}
     names.update({100 + i: "pre-bar " + o for i, o in enumerate(OPS)})
     names.update({200 + i: "post-bar " + o for i, o in enumerate(OPS)})
+    ids = marks[:, 0].tolist()
+    if 106 in ids and 100 in ids:
+        i0 = ids.index(106); i1 = ids.index(206); i2 = ids.index(100)
+        print(f"SAMPLE: barrier wait {(marks[i1,1]-marks[i0,1])/1e3:.2f} us, body {(marks[i2,1]-marks[i1,1])/1e3:.2f} us")
+        if 105 in ids:
+            i3 = ids.index(105); i4 = ids.index(205)
+            print(f"HEAD: barrier wait {(marks[i4,1]-marks[i3,1])/1e3:.2f} us; step (SAMPLE pre-bar -> HEAD post-bar) {(marks[i4,1]-marks[i0,1])/1e3:.1f} us")
+    if 206 in ids:
+        i1 = ids.index(206)
+        for i in range(i1 + 1, min(i1 + 8, len(marks))):
+            print(f"   {names.get(int(marks[i, 0]), marks[i, 0]):18s} +{int(marks[i, 1] - marks[i - 1, 1])}")
     sel = [i for i in range(len(marks)) if marks[i, 0] == 100]       # pre-barrier LN_QKV marks = layer starts
     if len(sel) > 4:
         a, b = sel[3], sel[4]
         print("marks of layer 3 (delta ns from previous mark):")
         for i in range(a, b + 1):
             print(f"   {names.get(int(marks[i, 0]), marks[i, 0]):18s} +{int(marks[i, 1] - marks[i - 1, 1])}")
+    if not t.any():
+        m.close(); sys.exit(0)
     before, after = t[:, 0], t[:, 1]
     wait = after - before                       # barrier wait seen by CTA 0
     work = np.append(before[1:], before[-1]) - after   # stage body on CTA 0 (until it reaches the next barrier)

@@ -17,15 +17,40 @@ constexpr int kVPerThread = (8448 + kConsumerThreads - 1) / kConsumerThreads;   
 
 __device__ __forceinline__ uint32_t key_of(float v) { return float_key(__float_as_uint(v)); }
 
-// Smallest key T in [lo, hi] such that pred(T) holds; pred monotone (false..false true..true), pred(hi) true.
-// count mode: pred(T) = #{key >= T} ... (see callers).  Implemented inline at the call sites.
+// Block reduction of K floats per thread with ONE bar.sync: per-warp shuffle trees, lane 0 parks the K warp sums in
+// `buf` ([kNW][K] floats; the caller alternates two buffers between consecutive calls so no second barrier is needed
+// against the next call's writes), then every thread adds the 8 warp sums in the fixed tree
+// ((w0+w4)+(w2+w6)) + ((w1+w5)+(w3+w7)).  Deterministic, and identical on every thread.
+template <int K>
+__device__ __forceinline__ void block_sum_k(float (&v)[K], float* buf) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < K; ++k) v[k] = warp_sum(v[k]);
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < K; ++k) buf[w * K + k] = v[k];
+  }
+  consumer_sync();
+#pragma unroll
+  for (int k = 0; k < K; ++k)
+    v[k] = ((buf[0 * K + k] + buf[4 * K + k]) + (buf[2 * K + k] + buf[6 * K + k])) +
+           ((buf[1 * K + k] + buf[5 * K + k]) + (buf[3 * K + k] + buf[7 * K + k]));
+}
+static_assert(kNW == 8, "block_sum_k hard-codes the 8-warp tree");
 
-// One sequence.  `sc` = V floats (scores), `ev` = V floats scratch, both shared.  All 512 consumer threads call.
+// One sequence.  All consumer threads call.  `sc` / `ev` (shared, V floats each) hold the processed scores and their
+// exponentials; thread t owns tokens t, t+256, ... in the selection passes (coalesced, conflict-free) and tokens
+// 33t .. 33t+32 in the vocabulary-ordered multinomial.  The passes are deliberately compact loops (unrolled x11, not
+// x33): this code runs once per step, so its instruction-cache footprint is paid as cold misses every time.
+constexpr int kSmpUnroll = 11;
+static_assert(kVPerThread % kSmpUnroll == 0, "sampler passes assume 3 x 11 elements per thread");
+
 static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int step_col) {
   Ctrl* c = sm.ctrl;
   float* sc = reinterpret_cast<float*>(sm.a_rm);
   float* ev = sm.red;
   float* scratch = c->scratch;
+  float* rbuf = ev + (8448 - 64);                    // 2 x [kNW][4] floats above the V exps (V <= 8256, tts_ar_create)
   const int tid = threadIdx.x;
   const int V = P.V;
   const int stop = P.stop_token;
@@ -43,22 +68,37 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
   const float* lg = P.logits + (size_t)lrow * P.v_stride;
   const uint32_t* seen = P.seen + (size_t)seq * P.seen_words;
   const float pen = P.rep_penalty;
+  const bool use_temp = P.do_sample && P.temperature != 1.0f;
 
   // scores = processors(logits): repetition penalty, then (sampling only) temperature
   float lmax = -INFINITY;
-  for (int v = tid; v < V; v += kConsumerThreads) {
-    float s = ld_cg_f(lg + v);
-    if (pen != 1.0f && ((__ldcg(seen + (v >> 5)) >> (v & 31)) & 1u)) s = (s < 0.f) ? s * pen : s / pen;
-    if (P.do_sample && P.temperature != 1.0f) s = s / P.temperature;
-    sc[v] = s;
-    lmax = fmaxf(lmax, s);
+#pragma unroll 1
+  for (int i0 = 0; i0 < kVPerThread; i0 += kSmpUnroll) {
+    float s[kSmpUnroll];
+#pragma unroll
+    for (int i = 0; i < kSmpUnroll; ++i) {
+      const int v = tid + (i0 + i) * kConsumerThreads;
+      s[i] = (v < V) ? ld_cg_f(lg + v) : -INFINITY;
+    }
+#pragma unroll
+    for (int i = 0; i < kSmpUnroll; ++i) {
+      const int v = tid + (i0 + i) * kConsumerThreads;
+      if (v < V) {
+        if (pen != 1.0f && ((__ldcg(seen + (v >> 5)) >> (v & 31)) & 1u)) s[i] = (s[i] < 0.f) ? s[i] * pen : s[i] / pen;
+        if (use_temp) s[i] = s[i] / P.temperature;
+        sc[v] = s[i];
+        lmax = fmaxf(lmax, s[i]);
+      }
+    }
   }
   const float smax = block_max(lmax, scratch);   // also orders the sc[] writes before the reads below
+  prof_mark(P, c, 31);
 
   int token;
   if (!P.do_sample) {
     // HF greedy: argmax of the processed scores; first index on ties (torch.argmax)
     int best = 0x7fffffff;
+#pragma unroll kSmpUnroll
     for (int v = tid; v < V; v += kConsumerThreads)
       if (sc[v] == smax) best = min(best, v);
     best = __reduce_min_sync(0xffffffffu, best);
@@ -69,49 +109,84 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
     token = __reduce_min_sync(0xffffffffu, b2);
   } else {
     uint32_t kmin = key_of(-INFINITY);             // keep key >= kmin
-    // ---- top-k: largest T with #{key >= T} >= k  ----
+    int par = 0;
+    // ---- top-k: largest T with #{key >= T} >= k  (4-way search: 3 probes per round) ----
     if (P.top_k > 0 && P.top_k < V) {
       uint32_t lo = key_of(-INFINITY), hi = key_of(smax);   // count(lo) = V >= k; answer in [lo, hi]
+      const float kf = (float)P.top_k;                      // counts <= 8448 are exact in fp32
       while (lo < hi) {
-        const uint32_t mid = lo + ((hi - lo + 1u) >> 1);
-        uint32_t cnt = 0;
-        for (int v = tid; v < V; v += kConsumerThreads) cnt += (key_of(sc[v]) >= mid) ? 1u : 0u;
-        cnt = block_sum_u32(cnt, scratch);
-        if (cnt >= (uint32_t)P.top_k) lo = mid; else hi = mid - 1u;
+        const uint32_t q = (hi - lo) >> 2;
+        uint32_t t[3];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) t[j] = q ? lo + q * (j + 1) : min(lo + 1u + j, hi);   // lo < t0 <= t1 <= t2 <= hi
+        float cnt[3] = {0.f, 0.f, 0.f};
+#pragma unroll kSmpUnroll
+        for (int v = tid; v < V; v += kConsumerThreads) {
+          const uint32_t k = key_of(sc[v]);
+#pragma unroll
+          for (int j = 0; j < 3; ++j) cnt[j] += (k >= t[j]) ? 1.f : 0.f;
+        }
+        block_sum_k<3>(cnt, rbuf + par * 32);
+        par ^= 1;
+        // pred(T) = count(T) >= k is true..true false..false in T; answer = largest T with pred
+        if (cnt[2] >= kf) lo = t[2];
+        else if (cnt[1] >= kf) { lo = t[1]; hi = t[2] - 1u; }
+        else if (cnt[0] >= kf) { lo = t[0]; hi = t[1] - 1u; }
+        else hi = t[0] - 1u;
       }
       kmin = lo;
     }
     // ---- e = exp(score - max) over the top-k survivors ----
-    float zloc = 0.f;
+    float zl[1] = {0.f};
+#pragma unroll kSmpUnroll
     for (int v = tid; v < V; v += kConsumerThreads) {
-      const float e = (key_of(sc[v]) >= kmin) ? expf(sc[v] - smax) : 0.f;
+      const float sv = sc[v];
+      const float e = (key_of(sv) >= kmin) ? expf(sv - smax) : 0.f;
       ev[v] = e;
-      zloc += e;
+      zl[0] += e;
     }
-    const float Z = block_sum(zloc, scratch);
-    // ---- top-p: smallest T with mass{key > T} < p * Z ; keep key >= T ----
+    block_sum_k<1>(zl, rbuf + par * 32);
+    par ^= 1;
+    const float Z = zl[0];
+    prof_mark(P, c, 32);
+    // ---- top-p: smallest T with mass{key > T} < p * Z ; keep key >= T  (4-way search) ----
     if (P.top_p < 1.0f) {
       const float lim = P.top_p * Z;
       uint32_t lo = kmin, hi = key_of(smax);        // pred(hi): mass above the max is 0 < lim
       while (lo < hi) {
-        const uint32_t mid = lo + ((hi - lo) >> 1);
-        float ms = 0.f;
-        for (int v = tid; v < V; v += kConsumerThreads) ms += (key_of(sc[v]) > mid) ? ev[v] : 0.f;
-        ms = block_sum(ms, scratch);
-        if (ms < lim) hi = mid; else lo = mid + 1u;
+        const uint32_t q = (hi - lo) >> 2;
+        uint32_t t[3];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) t[j] = q ? lo + q * (j + 1) - 1u : min(lo + j, hi);   // lo <= t0 <= t1 <= t2 <= hi
+        float ms[3] = {0.f, 0.f, 0.f};
+#pragma unroll kSmpUnroll
+        for (int v = tid; v < V; v += kConsumerThreads) {
+          const uint32_t k = key_of(sc[v]);
+          const float e = ev[v];
+#pragma unroll
+          for (int j = 0; j < 3; ++j) ms[j] += (k > t[j]) ? e : 0.f;
+        }
+        block_sum_k<3>(ms, rbuf + par * 32);
+        par ^= 1;
+        // pred(T) = mass{key > T} < lim is false..false true..true in T; answer = smallest T with pred
+        if (ms[0] < lim) hi = t[0];
+        else if (ms[1] < lim) { lo = t[0] + 1u; hi = t[1]; }
+        else if (ms[2] < lim) { lo = t[1] + 1u; hi = t[2]; }
+        else lo = t[2] + 1u;
       }
       kmin = lo;
     }
-    // ---- multinomial: inverse CDF in vocabulary order ----
+    consumer_sync();                               // ev[] complete before the vocabulary-ordered reads
+    prof_mark(P, c, 33);
+    // ---- multinomial: inverse CDF in vocabulary order (thread t owns tokens 33t .. 33t+32) ----
     const int v0 = tid * kVPerThread;
+    const int vend = min(v0 + kVPerThread, V);
     float loc = 0.f;
-#pragma unroll
-    for (int i = 0; i < kVPerThread; ++i) {
-      const int v = v0 + i;
-      if (v < V) {
-        const float e = (key_of(sc[v]) >= kmin) ? ev[v] : 0.f;
-        loc += e;
-      }
+#pragma unroll kSmpUnroll
+    for (int v = v0; v < vend; ++v) {
+      const float e = (key_of(sc[v]) >= kmin) ? ev[v] : 0.f;
+      ev[v] = e;                                   // own range only: kept mass, re-read below
+      loc += e;
     }
     // exclusive prefix over threads (fixed tree)
     const int lane = tid & 31, w = tid >> 5;
@@ -135,16 +210,13 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
     const float target = u01 * total;
     float run = wbase + incl - loc;
     int found = 0x7fffffff, lastkept = -1;
-#pragma unroll
-    for (int i = 0; i < kVPerThread; ++i) {
-      const int v = v0 + i;
-      if (v < V) {
-        const float e = (key_of(sc[v]) >= kmin) ? ev[v] : 0.f;
-        run += e;
-        if (e > 0.f) {
-          lastkept = v;
-          if (run > target && found == 0x7fffffff) found = v;
-        }
+#pragma unroll kSmpUnroll
+    for (int v = v0; v < vend; ++v) {
+      const float e = ev[v];
+      run += e;
+      if (e > 0.f) {
+        lastkept = v;
+        if (run > target && found == 0x7fffffff) found = v;
       }
     }
     found = __reduce_min_sync(0xffffffffu, found);
@@ -162,6 +234,7 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
     token = (f2 != 0x7fffffff) ? f2 : l2;
   }
 
+  prof_mark(P, c, 34);
   // ---- bookkeeping (sample_stream :1160-1190) + next-step embedding (unified_voice.py:212-214) ----
   const size_t oidx = (size_t)seq * P.out_stride + step_col;
   int tok = token;
@@ -196,6 +269,7 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
     x4[i] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
   }
   consumer_sync();   // sc / ev / scratch are reused by the next row
+  prof_mark(P, c, 35);
 }
 
 static __device__ void sample_stage(const Params& P, const Instr& ins, const Smem& sm, int step_col) {

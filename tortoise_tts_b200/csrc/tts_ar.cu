@@ -169,7 +169,7 @@ extern "C" int tts_ar_create(const TtsArConfig* cfg, TtsArHandle** out) {
   if (!cfg || !out) return fail(nullptr, TTS_AR_ERR_BAD_ARG, "null argument");
   if (cfg->struct_size != (int)sizeof(TtsArConfig)) return fail(nullptr, TTS_AR_ERR_BAD_ARG, "TtsArConfig.struct_size mismatch");
   if (cfg->model_dim != kD || cfg->n_heads != kH) return fail(nullptr, TTS_AR_ERR_BAD_ARG, "model_dim must be 1024 and n_heads 16");
-  if (cfg->n_layers < 1 || cfg->n_mel_codes < 2 || cfg->n_mel_codes > 8448 || cfg->max_utts < 1 || cfg->max_seqs < cfg->max_utts ||
+  if (cfg->n_layers < 1 || cfg->n_mel_codes < 2 || cfg->n_mel_codes > 8256 || cfg->max_utts < 1 || cfg->max_seqs < cfg->max_utts ||
       cfg->max_text_len < 1 || cfg->max_text_len + 2 > cfg->n_text_pos || cfg->max_new_tokens < 1 ||
       cfg->max_new_tokens + 2 > cfg->n_mel_pos || cfg->stop_mel_token >= cfg->n_mel_codes || cfg->start_mel_token >= cfg->n_mel_codes ||
       cfg->start_text_token >= cfg->n_text_rows || cfg->max_seqs > 1024)
