@@ -21,69 +21,67 @@ namespace tts {
 
 constexpr int kU4PerChunk = kChunkBytes / 16;
 
-// ---- barrier among the consumer warps of the 8 CTAs of a cluster (the producer warp never joins) ----------
-__device__ __forceinline__ bool cluster_barrier(Ctrl* c, uint32_t& cphase) {
-  consumer_sync();
-  if (threadIdx.x < kClusterSize) mbar_arrive_remote(&c->cbar, threadIdx.x);
-  bool ok = true;
-  if (!mbar_try_wait_cluster(&c->cbar, cphase)) {
-    const long long t0 = clock64();
-    while (!mbar_try_wait_cluster(&c->cbar, cphase)) {
-      if (c->abort_flag || clock64() - t0 > kWatchdogCycles) {
-        c->abort_flag = 1;
-        ok = false;
-        break;
-      }
-    }
-  }
-  cphase ^= 1u;
-  return ok;
+constexpr int kDecThreads = kConsumerThreads;     // 8 warps; there is no dedicated producer warp in this kernel
+
+// ---- hardware cluster barrier (all 256 threads of the 4 CTAs; ~0.2 us).  release/acquire at cluster scope: global
+// and distributed-shared writes made before it are visible to the cluster's threads after it. -----------------------
+__device__ __forceinline__ void cluster_barrier() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
-// ---- producer: this CTA's weight chunks of the whole launch, in consumption order --------------------------
-__device__ void dec_producer(const Params& P, Ctrl* c, uint8_t* ring, int head, int rank) {
-  if ((threadIdx.x & 31) != 0) return;
-  const uint64_t pol = make_evict_first_policy();
-  const int cta = blockIdx.x;
-  uint32_t pi = 0, slot = 0, round = 0;
-  bool stopped = false;
-  auto issue = [&](const uint4* src) {
-    if (stopped) return;
-    if (round > 0) {
-      const uint32_t par = (round - 1) & 1;
-      const long long t_start = clock64();
-      while (!mbar_try_wait(&c->empty[slot], par)) {
-        if (c->stop_flag || c->abort_flag) { stopped = true; return; }
-        if (clock64() - t_start > kWatchdogCycles) { c->abort_flag = 1; stopped = true; return; }
-      }
+// ---- weight feed: thread 0 of the CTA keeps the bulk-copy ring full --------------------------------------------------
+// The chunk sequence of the whole launch is fixed (per layer: 6 c_attn, 2 split-K c_proj, 4 c_fc, 4 mlp.c_proj chunks;
+// then this CTA's mel-head chunks), so instead of a producer warp waiting on "slot empty" barriers, every stage that has
+// finished reading k ring slots (after a CTA barrier) lets thread 0 issue the next k chunks of the sequence into exactly
+// those slots.  The ring is therefore always n_slots chunks (more than half a layer) ahead of the consumers, across
+// grid barriers, steps and the sampler.
+struct Feed {
+  int step, layer, idx;      // cursor in the chunk sequence (thread 0 only)
+  int passes;                // model passes of this launch
+  uint32_t slot, issued;
+  uint64_t pol;
+};
+
+__device__ __forceinline__ void feed_init(const Params& P, Feed& f) {
+  f.step = 0; f.layer = 0; f.idx = 0;
+  f.passes = P.n_steps - (P.skip_last_model ? 1 : 0);
+  f.slot = 0; f.issued = 0;
+  f.pol = make_evict_first_policy();
+}
+
+// Issue the next n chunks (thread 0 only; the n slots at the feed cursor must be free).
+__device__ __forceinline__ void feed(const Params& P, Ctrl* c, uint8_t* ring, Feed& f, int n, int head, int rank, int ht0,
+                                     int hcnt) {
+  for (int k = 0; k < n && f.step < f.passes; ++k) {
+    const uint4* src;
+    if (f.layer < P.n_layers) {
+      const LayerDev& L = P.layers[f.layer];
+      const int i = f.idx;
+      if (i < 6) src = L.w_qkv + (size_t)((i >> 1) * (kD / 8) + head * 8 + 2 * rank + (i & 1)) * kU4PerChunk;
+      else if (i < 8) src = L.w_projk + (size_t)(head * 8 + 2 * rank + (i - 6)) * kU4PerChunk;
+      else if (i < 12) src = L.w_fc + (size_t)(blockIdx.x * 4 + (i - 8)) * kU4PerChunk;
+      else src = L.w_proj2 + (size_t)(blockIdx.x * 4 + (i - 12)) * kU4PerChunk;
+      if (++f.idx == 16) { f.idx = 0; ++f.layer; }
+    } else {
+      src = P.w_head + (size_t)(ht0 + f.idx) * kU4PerChunk;
+      if (++f.idx == hcnt) { f.idx = 0; f.layer = 0; ++f.step; }
     }
-    mbar_arrive_expect_tx(&c->full[slot], kChunkBytes);
-    bulk_g2s(ring + (size_t)slot * kChunkBytes, src, kChunkBytes, &c->full[slot], pol);
-    ++pi;
-    if (++slot == (uint32_t)P.n_slots) { slot = 0; ++round; }
-  };
-  int ht0, hcnt;
-  tile_range(P.v_tiles, P.G, 0, cta, &ht0, &hcnt);
-  for (int step = 0; step < P.n_steps && !stopped; ++step) {
-    if (P.skip_last_model && step == P.n_steps - 1) break;
-    for (int layer = 0; layer < P.n_layers && !stopped; ++layer) {
-      const LayerDev& L = P.layers[layer];
-      for (int i = 0; i < 6; ++i) issue(L.w_qkv + (size_t)((i >> 1) * (kD / 8) + head * 8 + 2 * rank + (i & 1)) * kU4PerChunk);
-      for (int i = 0; i < 2; ++i) issue(L.w_projk + (size_t)(head * 8 + 2 * rank + i) * kU4PerChunk);
-      for (int i = 0; i < 4; ++i) issue(L.w_fc + (size_t)(cta * 4 + i) * kU4PerChunk);
-      for (int i = 0; i < 4; ++i) issue(L.w_proj2 + (size_t)(cta * 4 + i) * kU4PerChunk);
-    }
-    for (int i = 0; i < hcnt; ++i) issue(P.w_head + (size_t)(ht0 + i) * kU4PerChunk);
-  }
-  // Drain: never leave the kernel with bulk copies still landing in this CTA's shared memory.
-  const long long t_start = clock64();
-  while (!c->stop_flag) {
-    if (c->abort_flag || clock64() - t_start > kWatchdogCycles) return;
-  }
-  for (uint32_t k = c->stop_ci; k < pi; ++k) {
-    if (!mbar_wait(&c->full[k % P.n_slots], (k / P.n_slots) & 1, &c->abort_flag)) return;
+    mbar_arrive_expect_tx(&c->full[f.slot], kChunkBytes);
+    bulk_g2s(ring + (size_t)f.slot * kChunkBytes, src, kChunkBytes, &c->full[f.slot], f.pol);
+    ++f.issued;
+    if (++f.slot == (uint32_t)P.n_slots) f.slot = 0;
   }
 }
+
+// What the stages need to refill the ring: called by ALL threads right after a CTA barrier that follows the reads.
+// Refills are issued by thread 0 at the grid barriers (dec_grid_barrier), right after its arrival: the SM's L2 read
+// port (~64 B/clk) then carries the 64-128 KiB of refill while the CTA waits for the other CTAs anyway, instead of
+// competing with the latency-critical loads of the stage bodies (LayerNorm rows, biases, K/V, A fragments).
+struct Feeder {
+  Feed f;
+  int head, rank, ht0, hcnt;
+  int pending;               // ring slots read to the end since the last refill (uniform across the CTA's threads)
+};
 
 // ---- per-step row facts of this CTA, kept in shared memory (upper part of the reduction buffer) ----------------
 // Positions and page tables do not change inside a step, so the dependent global loads
@@ -302,6 +300,7 @@ __device__ void attn_local(const Params& P, int layer, int head, int rbase, cons
         }
       }
     }
+    prof_mark(P, sm.ctrl, 12);
     float* pp = part + w * kPartStride;
     if (rg == 0) {
       *reinterpret_cast<float4*>(pp + 8 + dc * 8) = make_float4(acc[0], acc[1], acc[2], acc[3]);
@@ -334,6 +333,7 @@ __device__ void attn_local(const Params& P, int layer, int head, int rbase, cons
     }
     write_ctx_pair(P, row, head * kHD + 2 * lane, o0, o1);
   }
+  prof_mark(P, sm.ctrl, 13);
 }
 
 // ---- 16-row GEMM over this CTA's next `cnt` (<= NT) streamed K=1024 chunks ------------------------------------------
@@ -341,10 +341,25 @@ __device__ void attn_local(const Params& P, int layer, int head, int rbase, cons
 // are loaded once), the 8 partial tiles are summed through shared memory in a fixed order (deterministic).
 // HALF: only rows [row_lo, row_lo + 8) are produced (c_attn: the other half belongs to the sibling cluster).
 // epi(row, col, v0, v1) receives the fp32 sums of columns col, col+1 (col = 8 * tile_of(i) + even offset).
+// `bias` (indexed by output column) is fetched before the mma loop for the (at most two) pairs a thread finishes.
 template <int NT, bool HALF, typename TileFn, typename Epi>
-__device__ __forceinline__ void gemm16(const Smem& sm, Pipe& pipe, int cnt, int row_lo, TileFn tile_of, Epi epi) {
+__device__ __forceinline__ void gemm16(const Params& P, const Smem& sm, Pipe& pipe, Feeder& fd, int cnt, int row_lo, const float* bias,
+                                       TileFn tile_of, Epi epi) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   Ctrl* c = sm.ctrl;
+  constexpr int kPerTile = HALF ? 32 : 64;
+  constexpr int kMaxE = (NT * kPerTile + kConsumerThreads - 1) / kConsumerThreads;
+  float2 bpre[kMaxE];
+#pragma unroll
+  for (int k = 0; k < kMaxE; ++k) {
+    const int e = threadIdx.x + k * kConsumerThreads;
+    bpre[k] = make_float2(0.f, 0.f);
+    if (e < cnt * kPerTile) {
+      const int t = e / kPerTile, rem = e - t * kPerTile;
+      const int ln = HALF ? rem : (rem >> 1);
+      bpre[k] = *reinterpret_cast<const float2*>(bias + tile_of(t) * 8 + 2 * (ln & 3));
+    }
+  }
   uint4 a[8];
   {
     const uint32_t base = smem_u32(sm.a_rm) + (uint32_t)(((lane & 7) + ((lane >> 3) & 1) * 8) * kARowBytes) +
@@ -386,15 +401,8 @@ __device__ __forceinline__ void gemm16(const Smem& sm, Pipe& pipe, int cnt, int 
       }
       p2.advance();
     }
-  __syncwarp();
-  if (lane == 0) {
-    Pipe p3 = pipe;
-    for (int t = 0; t < cnt; ++t) {
-      mbar_arrive(&c->empty[p3.slot]);
-      p3.advance();
-    }
-  }
   pipe = p2;
+  prof_mark(P, c, 2);
   float4* red4 = reinterpret_cast<float4*>(sm.red);
 #pragma unroll
   for (int t = 0; t < NT; ++t)
@@ -402,9 +410,14 @@ __device__ __forceinline__ void gemm16(const Smem& sm, Pipe& pipe, int cnt, int 
       red4[(w * NT + t) * 32 + lane] = make_float4(acc[t][0][0] + acc[t][1][0], acc[t][0][1] + acc[t][1][1],
                                                    acc[t][0][2] + acc[t][1][2], acc[t][0][3] + acc[t][1][3]);
   consumer_sync();
+  prof_mark(P, c, 4);
+  fd.pending += cnt;                     // every warp is done with the cnt ring slots; refilled at the next grid barrier
   const float2* red2 = reinterpret_cast<const float2*>(sm.red);
-  const int per_tile = HALF ? 32 : 64;
-  for (int e = threadIdx.x; e < cnt * per_tile; e += kConsumerThreads) {
+  const int per_tile = kPerTile;
+#pragma unroll
+  for (int q = 0; q < kMaxE; ++q) {
+    const int e = threadIdx.x + q * kConsumerThreads;
+    if (e >= cnt * per_tile) break;
     const int t = e / per_tile, rem = e - t * per_tile;
     const int ln = HALF ? rem : (rem >> 1);
     const int hh = HALF ? (row_lo >> 3) : (rem & 1);
@@ -415,8 +428,9 @@ __device__ __forceinline__ void gemm16(const Smem& sm, Pipe& pipe, int cnt, int 
       s0 += v.x;
       s1 += v.y;
     }
-    epi((ln >> 2) + 8 * hh, tile_of(t) * 8 + 2 * (ln & 3), s0, s1);
+    epi((ln >> 2) + 8 * hh, tile_of(t) * 8 + 2 * (ln & 3), s0 + bpre[q].x, s1 + bpre[q].y);
   }
+  prof_mark(P, c, 3);
   consumer_sync();
 }
 
@@ -465,8 +479,6 @@ __device__ void proj_splitk(const Params& P, int layer, int head, int rank, int 
         }
       }
     }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&c->empty[pipe.slot]);
     pipe.advance();
     if (row_ok) {
 #pragma unroll
@@ -480,49 +492,132 @@ __device__ void proj_splitk(const Params& P, int layer, int head, int rank, int 
   }
 }
 
+// ---- mlp.c_proj: x[:, 8c .. 8c+8) = y + h . W[:, 8c ..] + bias ; y handed back zeroed -----------------------------------
+// One n8-tile per CTA, K = 4096 = 4 streamed chunks; warp w owns k16-blocks 8w..8w+7 of every chunk.  All 32 A
+// fragments of the warp (h is bf16 in mma A-fragment order in global memory, L2-resident) are requested before the
+// first mma, so the stage costs one L2 round trip instead of one per chunk.
+__device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pipe, Feeder& fd) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  Ctrl* c = sm.ctrl;
+  const uint4* a_gl = reinterpret_cast<const uint4*>(P.hbuf) + (size_t)(w * 8) * 32 + lane;   // m-tile 0
+  uint4 a[32];
+#pragma unroll
+  for (int q = 0; q < 4; ++q)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a[q * 8 + i] = ld_cg_u4(a_gl + (size_t)(q * kKbPerChunk + i) * 32);
+  // epilogue operands of the threads that own an output pair (64 pairs: 16 rows x 4 column pairs)
+  const int col = blockIdx.x * 8 + 2 * ((threadIdx.x >> 1) & 3);
+  const int erow = (threadIdx.x >> 3) + 8 * (threadIdx.x & 1);
+  const bool owner = threadIdx.x < 64 && erow < P.n_rows;
+  longlong2 old = make_longlong2(0ll, 0ll);
+  float2 bias = make_float2(0.f, 0.f);
+  if (owner) {
+    old = ld_cg_ll2(P.y + (size_t)erow * kD + col);
+    bias = *reinterpret_cast<const float2*>(P.layers[layer].b_proj2 + col);
+  }
+  float acc[2][4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) acc[0][j] = acc[1][j] = 0.f;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    mbar_wait(&c->full[pipe.slot], pipe.phase, &c->abort_flag);
+    const uint4* bsm = reinterpret_cast<const uint4*>(sm.ring + (size_t)pipe.slot * kChunkBytes) + (w * 4) * 32 + lane;
+#pragma unroll
+    for (int s2 = 0; s2 < 4; ++s2) {
+      const uint4 b = bsm[s2 * 32];
+      mma_bf16_16816(acc[s2 & 1], a[q * 8 + 2 * s2], b.x, b.y);
+      mma_bf16_16816(acc[s2 & 1], a[q * 8 + 2 * s2 + 1], b.z, b.w);
+    }
+    pipe.advance();
+  }
+  float4* red4 = reinterpret_cast<float4*>(sm.red);
+  red4[w * 32 + lane] = make_float4(acc[0][0] + acc[1][0], acc[0][1] + acc[1][1], acc[0][2] + acc[1][2], acc[0][3] + acc[1][3]);
+  consumer_sync();
+  fd.pending += 4;
+  if (owner) {
+    const float2* red2 = reinterpret_cast<const float2*>(sm.red);
+    const int ln = threadIdx.x >> 1, hh = threadIdx.x & 1;
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int k = 0; k < kNW; ++k) {
+      const float2 v = red2[(k * 32 + ln) * 2 + hh];
+      s0 += v.x;
+      s1 += v.y;
+    }
+    *reinterpret_cast<float2*>(P.x + (size_t)erow * kD + col) =
+        make_float2(from_fixed(old.x) + s0 + bias.x, from_fixed(old.y) + s1 + bias.y);
+    *reinterpret_cast<longlong2*>(P.y + (size_t)erow * kD + col) = make_longlong2(0ll, 0ll);
+  }
+}
+
+// ---- grid-wide barrier of this kernel ---------------------------------------------------------------------------------
+// Same counter protocol as ar_core.cuh grid_barrier.  Thread 0 also refills `refill_n` ring slots while it waits.
+// Acquire side: everything other CTAs write during the launch is read with ld.global.cg (L2, the coherence point)
+// and those loads are issued after the poll load has returned the final count, so no gpu-scope fence (and no L1
+// invalidate) is needed after the poll; TTS_AR_DBG bit 1 puts the fence back (A/B switch).
+__device__ __forceinline__ bool dec_grid_barrier(const Params& P, const Smem& sm, uint32_t& epoch, Feeder& fd, int extra) {
+  Ctrl* c = sm.ctrl;
+  consumer_sync();
+  ++epoch;
+  const int refill_n = fd.pending + extra;
+  fd.pending = 0;
+  if (threadIdx.x == 0) {
+    red_release_add_u32(P.bar_counter, 1u);
+    if (refill_n) feed(P, c, sm.ring, fd.f, refill_n, fd.head, fd.rank, fd.ht0, fd.hcnt);
+    const uint32_t target = epoch * (uint32_t)P.G;
+    const long long t0 = clock64();
+    uint32_t spins = 0;
+    while (ld_relaxed_u32(P.bar_counter) < target) {
+      if ((++spins & 255u) == 0) {
+        if (c->abort_flag || __ldcg(P.watchdog) || clock64() - t0 > kWatchdogCycles) {
+          c->abort_flag = 1;
+          *reinterpret_cast<volatile int*>(P.watchdog) = 1;
+          break;
+        }
+      }
+    }
+    if (P.dbg_flags & 2) fence_acq_rel_gpu();
+  }
+  consumer_sync();
+  return c->abort_flag == 0;
+}
+
 // ---- the kernel ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 1) ar_decode_kernel(const __grid_constant__ Params P) {
+__global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_constant__ Params P) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const Smem sm = carve_smem(smem_raw, 1);
   Ctrl* c = sm.ctrl;
   const int rank = (int)cluster_ctarank();
   const int head = (int)cluster_id_x() >> 1;
   const int row_lo = ((int)cluster_id_x() & 1) * 8;
+  Feeder fd;
+  fd.head = head; fd.rank = rank; fd.pending = 0;
+  tile_range(P.v_tiles, P.G, 0, blockIdx.x, &fd.ht0, &fd.hcnt);
   if (threadIdx.x == 0) {
-    for (int i = 0; i < P.n_slots; ++i) {
-      mbar_init(&c->full[i], 1);
-      mbar_init(&c->empty[i], kNW);
-    }
-    mbar_init(&c->cbar, kClusterSize);
+    for (int i = 0; i < P.n_slots; ++i) mbar_init(&c->full[i], 1);
     c->abort_flag = 0;
     c->ibuf[0] = 0;
     c->ibuf[1] = 0;
-    c->stop_flag = 0;
-    c->stop_ci = 0;
     fence_mbar_init();
+    feed_init(P, fd.f);
+    feed(P, c, sm.ring, fd.f, P.n_slots, head, rank, fd.ht0, fd.hcnt);
   }
   __syncthreads();
-  cluster_sync_all();          // every CTA's cbar is initialised before anyone arrives on it remotely
-
-  if (threadIdx.x >= kConsumerThreads) {
-    dec_producer(P, c, sm.ring, head, rank);
-    return;
-  }
+  cluster_sync_all();          // all CTAs of the cluster are running before anyone writes into a peer's shared memory
 
   Pipe pipe;
   pipe.ci = 0; pipe.slot = 0; pipe.phase = 0; pipe.n_slots = P.n_slots;
-  uint32_t epoch = 0, cphase = 0;
+  uint32_t epoch = 0;
   int steps_done = 0;
   bool alive = true;
   const int n = P.n_rows;
-  int ht0, hcnt;
-  tile_range(P.v_tiles, P.G, 0, blockIdx.x, &ht0, &hcnt);
+  const int ht0 = fd.ht0, hcnt = fd.hcnt;
   Instr ins;
   ins.row0 = 0; ins.nrows = n; ins.flags = 0; ins.rot = 0; ins.pad0 = ins.pad1 = 0;
   for (int step = 0; step < P.n_steps && alive; ++step) {
     if (blockIdx.x == 0 && threadIdx.x == 0) c->ibuf[1] = (P.prof && step == P.prof_step) ? 1 : 0;
     prof_mark(P, c, 100 + OP_SAMPLE);
-    alive = grid_barrier(P, c, epoch);
+    alive = dec_grid_barrier(P, sm, epoch, fd, 0);
     if (!alive) break;
     prof_mark(P, c, 200 + OP_SAMPLE);
     ins.op = OP_SAMPLE; ins.layer = 0; ins.nrows = P.n_seqs;
@@ -534,31 +629,27 @@ __global__ void __launch_bounds__(kThreads, 1) ar_decode_kernel(const __grid_con
       ins.layer = layer;
       // ---- phase A: ln_1 -> q,k,v of this head -> attention -> split-K c_proj -> y ----
       prof_mark(P, c, 100 + OP_LN_QKV);
-      alive = grid_barrier(P, c, epoch);
+      alive = dec_grid_barrier(P, sm, epoch, fd, 0);
       if (!alive) break;
       prof_mark(P, c, 200 + OP_LN_QKV);
       if (layer == 0 && ld_cg_i(P.n_active) == 0) { alive = false; break; }
       if (layer == 0) build_rinfo(P, row_lo + 2 * rank, sm);
       ins.op = OP_LN_QKV; ins.flags = 0;
-      const bool ln_local = P.dbg_flags & 1;
-      if (!ln_local) {
-        ln_cluster<false>(P, ins, sm, P.x, P.layers[layer].ln1_g, P.layers[layer].ln1_b, nullptr, nullptr, rank, head, layer + 1);
-        if (!(alive = cluster_barrier(c, cphase))) break;
-        prof_mark(P, c, 1);
-      }
-      if (ln_local) {
-        ins.flags = F_ROW_RANGE; ins.pad0 = row_lo; ins.pad1 = row_lo + 8;
-        gemm_tiles<1>(P, ins, sm, pipe, head * 8 + 2 * rank, 6, kD / 8, 2, P.x, false);
-        ins.flags = 0;
+      if (P.dbg_flags & 1) {
+        ln_rows_to_smem<false>(P, ins, sm.a_rm, P.x, P.layers[layer].ln1_g, P.layers[layer].ln1_b, nullptr, nullptr, 1);
+        consumer_sync();
       } else {
+        ln_cluster<false>(P, ins, sm, P.x, P.layers[layer].ln1_g, P.layers[layer].ln1_b, nullptr, nullptr, rank, head, layer + 1);
+        cluster_barrier();
+      }
+      prof_mark(P, c, 1);
+      {
         const float* bias = P.layers[layer].b_qkv;
         const int* ri = rinfo_ptr(sm);
         const int t0 = head * 8 + 2 * rank;
-        gemm16<6, true>(sm, pipe, 6, row_lo, [&](int i) { return t0 + (i >> 1) * (kD / 8) + (i & 1); },
+        gemm16<6, true>(P, sm, pipe, fd, 6, row_lo, bias, [&](int i) { return t0 + (i >> 1) * (kD / 8) + (i & 1); },
                         [&](int row, int col, float v0, float v1) {
                           if (row >= n) return;
-                          v0 += bias[col];
-                          v1 += bias[col + 1];
                           const int part = col >> 10, cc = col & (kD - 1);
                           if (part == 0) {   // query, pre-scaled by 1/sqrt(64) (exact: power of two)
                             *reinterpret_cast<float2*>(P.q + (size_t)row * kD + cc) = make_float2(v0 * 0.125f, v1 * 0.125f);
@@ -570,69 +661,72 @@ __global__ void __launch_bounds__(kThreads, 1) ar_decode_kernel(const __grid_con
                           }
                         });
       }
-      if (!(alive = cluster_barrier(c, cphase))) break;
+      cluster_barrier();
       prof_mark(P, c, 200 + OP_ATTN);
       attn_local(P, layer, head, row_lo + 2 * rank, sm);
-      if (!(alive = cluster_barrier(c, cphase))) break;
+      cluster_barrier();
       prof_mark(P, c, 200 + OP_PROJ);
       proj_splitk(P, layer, head, rank, row_lo, sm, pipe);
       // ---- phase B: ln_2 -> c_fc -> gelu_new ----
       prof_mark(P, c, 100 + OP_LN_FC);
-      alive = grid_barrier(P, c, epoch);
+      alive = dec_grid_barrier(P, sm, epoch, fd, 2);     // + the two split-K c_proj slots
       if (!alive) break;
       prof_mark(P, c, 200 + OP_LN_FC);
       ins.op = OP_LN_FC; ins.flags = F_FIXED_SRC;
-      if (!ln_local) {
-        ln_cluster<false>(P, ins, sm, P.x, P.layers[layer].ln2_g, P.layers[layer].ln2_b, nullptr, nullptr, rank, head, -1);
-        if (!(alive = cluster_barrier(c, cphase))) break;
-        prof_mark(P, c, 1);
-      }
-      if (ln_local) {
-        gemm_tiles<1>(P, ins, sm, pipe, blockIdx.x * 4, 4, 0, 1 << 30, P.x, false);
+      if (P.dbg_flags & 1) {
+        ln_rows_to_smem<false>(P, ins, sm.a_rm, P.x, P.layers[layer].ln2_g, P.layers[layer].ln2_b, nullptr, nullptr, 1);
+        consumer_sync();
       } else {
+        ln_cluster<false>(P, ins, sm, P.x, P.layers[layer].ln2_g, P.layers[layer].ln2_b, nullptr, nullptr, rank, head, -1);
+        cluster_barrier();
+      }
+      prof_mark(P, c, 1);
+      {
         const float* bias = P.layers[layer].b_fc;
         const int t0 = blockIdx.x * 4;
-        gemm16<4, false>(sm, pipe, 4, 0, [&](int i) { return t0 + i; }, [&](int row, int col, float v0, float v1) {
+        gemm16<4, false>(P, sm, pipe, fd, 4, 0, bias, [&](int i) { return t0 + i; }, [&](int row, int col, float v0, float v1) {
           if (row >= n) return;
-          const float h0 = gelu_new(v0 + bias[col]), h1 = gelu_new(v1 + bias[col + 1]);
+          const float h0 = gelu_new(v0), h1 = gelu_new(v1);
           *reinterpret_cast<uint32_t*>(P.hbuf + afrag_elem_offset(row, col, kD4)) = pack_bf16x2(h0, h1);
         });
       }
       // ---- phase C: mlp.c_proj, x = y + . ----
       prof_mark(P, c, 100 + OP_PROJ2);
-      alive = grid_barrier(P, c, epoch);
+      alive = dec_grid_barrier(P, sm, epoch, fd, 0);
       if (!alive) break;
       prof_mark(P, c, 200 + OP_PROJ2);
-      ins.op = OP_PROJ2; ins.flags = 0;
-      gemm_tiles<1>(P, ins, sm, pipe, blockIdx.x, 1, 0, 1 << 30, nullptr);
+      proj2_stage(P, layer, sm, pipe, fd);
       if (c->abort_flag) alive = false;
     }
     if (!alive) break;
     prof_mark(P, c, 100 + OP_HEAD);
-    alive = grid_barrier(P, c, epoch);
+    alive = dec_grid_barrier(P, sm, epoch, fd, 0);
     if (!alive) break;
     prof_mark(P, c, 200 + OP_HEAD);
     ins.op = OP_HEAD; ins.layer = 0; ins.flags = 0;
     ln_cluster<true>(P, ins, sm, P.x, P.lnf_g, P.lnf_b, P.fn_g, P.fn_b, rank, head, 0);
-    if (!(alive = cluster_barrier(c, cphase))) break;
+    cluster_barrier();
     for (int tb = 0; tb < hcnt; tb += 6) {
       const int t0 = ht0 + tb;
-      gemm16<6, false>(sm, pipe, min(6, hcnt - tb), 0, [&](int i) { return t0 + i; }, [&](int row, int col, float v0, float v1) {
-        if (row >= n) return;
-        float* lp = P.logits + (size_t)row * P.v_stride + col;
-        if (col < P.V) lp[0] = v0 + P.b_head[col];
-        if (col + 1 < P.V) lp[1] = v1 + P.b_head[col + 1];
-      });
+      gemm16<6, false>(P, sm, pipe, fd, min(6, hcnt - tb), 0, P.b_head, [&](int i) { return t0 + i; },
+                       [&](int row, int col, float v0, float v1) {
+                         if (row >= n) return;
+                         float* lp = P.logits + (size_t)row * P.v_stride + col;     // b_head is zero-padded to v_stride
+                         if (col < P.V) lp[0] = v0;
+                         if (col + 1 < P.V) lp[1] = v1;
+                       });
     }
     if (c->abort_flag) alive = false;
   }
   consumer_sync();
   if (threadIdx.x == 0) {
     if (blockIdx.x == 0) *P.steps_done = steps_done;
-    c->stop_ci = pipe.ci;
-    __threadfence_block();
-    c->stop_flag = 1;
+    // never leave the kernel with bulk copies still landing in this CTA's shared memory
+    for (uint32_t k = pipe.ci; k < fd.f.issued; ++k)
+      if (!mbar_wait(&c->full[k % P.n_slots], (k / P.n_slots) & 1, &c->abort_flag)) break;
   }
+  __syncthreads();
+  cluster_sync_all();          // nobody exits while a peer could still address its shared memory
 }
 
 // ---- attn.c_proj -> split-K chunks (layout.h projk_elem_offset); src = HF Conv1D weight [1024 in, 1024 out] ----
@@ -669,7 +763,7 @@ static cudaError_t decode_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* a
   }
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(kDecCtas);
-  cfg.blockDim = dim3(kThreads);
+  cfg.blockDim = dim3(kDecThreads);
   cfg.dynamicSmemBytes = (size_t)smem_bytes;
   cfg.stream = st;
   attrs[0].id = cudaLaunchAttributeClusterDimension;
@@ -679,7 +773,9 @@ static cudaError_t decode_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* a
   attrs[1].id = cudaLaunchAttributeCooperative;
   attrs[1].val.cooperative = 1;
   cfg.attrs = attrs;
-  cfg.numAttrs = 2;
+  // TTS_AR_NOCOOP: plain cluster launch (profilers that cannot replay cooperative launches); the 128 CTAs are
+  // still co-resident on an otherwise idle B200 and every device-side wait is watchdogged.
+  cfg.numAttrs = getenv("TTS_AR_NOCOOP") ? 1 : 2;
   return cudaSuccess;
 }
 
