@@ -55,12 +55,12 @@ __device__ __forceinline__ void feed(const Params& P, Ctrl* c, uint8_t* ring, Fe
   for (int k = 0; k < n && f.step < f.passes; ++k) {
     const uint4* src;
     if (f.layer < P.n_layers) {
-      const LayerDev& L = P.layers[f.layer];
+      const uint4* L = layer_w(P, f.layer);
       const int i = f.idx;
-      if (i < 6) src = L.w_qkv + (size_t)((i >> 1) * (kD / 8) + head * 8 + 2 * rank + (i & 1)) * kU4PerChunk;
-      else if (i < 8) src = L.w_projk + (size_t)(head * 8 + 2 * rank + (i - 6)) * kU4PerChunk;
-      else if (i < 12) src = L.w_fc + (size_t)(blockIdx.x * 4 + (i - 8)) * kU4PerChunk;
-      else src = L.w_proj2 + (size_t)(blockIdx.x * 4 + (i - 12)) * kU4PerChunk;
+      if (i < 6) src = L + (size_t)((i >> 1) * (kD / 8) + head * 8 + 2 * rank + (i & 1)) * kU4PerChunk;
+      else if (i < 8) src = L + kOffProjk + (size_t)(head * 8 + 2 * rank + (i - 6)) * kU4PerChunk;
+      else if (i < 12) src = L + kOffFc + (size_t)(blockIdx.x * 4 + (i - 8)) * kU4PerChunk;
+      else src = L + kOffProj2 + (size_t)(blockIdx.x * 4 + (i - 12)) * kU4PerChunk;
       if (++f.idx == 16) { f.idx = 0; ++f.layer; }
     } else {
       src = P.w_head + (size_t)(ht0 + f.idx) * kU4PerChunk;
@@ -161,7 +161,7 @@ __device__ void ln_cluster(const Params& P, const Instr& ins, const Smem& sm, co
     if (t == 0) {
       if (pf_layer < P.n_layers) {
         constexpr int kPer = ((4 * kD + kD3 + kD + kD4 + kD) * 4 / kDecCtas + 15) / 16 * 16;   // 416 B
-        bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(P.layers[pf_layer].ln1_g) + (size_t)blockIdx.x * kPer, kPer);
+        bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(layer_f(P, pf_layer)) + (size_t)blockIdx.x * kPer, kPer);
       } else {
         const int per = ((4 * kD + P.v_stride) * 4 / kDecCtas + 15) / 16 * 16;
         bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(P.lnf_g) + (size_t)blockIdx.x * per, per);
@@ -184,7 +184,7 @@ __device__ void ln_cluster(const Params& P, const Instr& ins, const Smem& sm, co
 // ---- attention of head `head` for rows rbase, rbase+1 ------------------------------------------------------------
 // Warp w: row rbase + (w >> 2), quarter (w & 3) of the row's 16-position granules (a granule never straddles a
 // page).  K/V granules are double-buffered in registers so the next granule's 128-bit loads are in flight while
-// the current one is reduced; the four partial (max, sum, acc) states of a row are merged in shared memory.
+// earlier ones are reduced; the four partial (max, sum, acc) states of a row are merged in shared memory.
 struct Gran {
   uint4 k[4], v[4];
   int cnt;
@@ -276,8 +276,9 @@ __device__ void attn_local(const Params& P, int layer, int head, int rbase, cons
       if (g1 > g0) {
         const int* pt = ri + 64 + 64 * j;
         const __nv_bfloat16* kvb = P.kv + kv_row_offset(layer, P.n_pages, 0, 0, head, 0) + dc * 8;
-        Gran A, B;
+        Gran A, B, C;                                  // three granules in flight per warp (12 KiB)
         gran_load(A, kvb, pt, g0, Gp, plen, len, rg);
+        if (g0 + 1 < g1) gran_load(B, kvb, pt, g0 + 1, Gp, plen, len, rg);
         float qv[8];
         {
           const float* qp = P.q + (size_t)row * kD + head * kHD + dc * 8;
@@ -285,11 +286,17 @@ __device__ void attn_local(const Params& P, int layer, int head, int rbase, cons
           qv[0] = a.x * kLog2e; qv[1] = a.y * kLog2e; qv[2] = a.z * kLog2e; qv[3] = a.w * kLog2e;
           qv[4] = b.x * kLog2e; qv[5] = b.y * kLog2e; qv[6] = b.z * kLog2e; qv[7] = b.w * kLog2e;
         }
-        for (int g = g0; g < g1; g += 2) {
-          if (g + 1 < g1) gran_load(B, kvb, pt, g + 1, Gp, plen, len, rg);
+        for (int g = g0; g < g1; g += 3) {
+          if (g + 2 < g1) gran_load(C, kvb, pt, g + 2, Gp, plen, len, rg);
           gran_reduce(A, qv, rg, m, l, acc);
-          if (g + 2 < g1) gran_load(A, kvb, pt, g + 2, Gp, plen, len, rg);
-          if (g + 1 < g1) gran_reduce(B, qv, rg, m, l, acc);
+          if (g + 1 < g1) {
+            if (g + 3 < g1) gran_load(A, kvb, pt, g + 3, Gp, plen, len, rg);
+            gran_reduce(B, qv, rg, m, l, acc);
+          }
+          if (g + 2 < g1) {
+            if (g + 4 < g1) gran_load(B, kvb, pt, g + 4, Gp, plen, len, rg);
+            gran_reduce(C, qv, rg, m, l, acc);
+          }
         }
         l += __shfl_xor_sync(0xffffffffu, l, 8);
         l += __shfl_xor_sync(0xffffffffu, l, 16);
@@ -457,7 +464,7 @@ __device__ void proj_splitk(const Params& P, int layer, int head, int rank, int 
     for (int tt = 0; tt < 2; ++tt) {
       add[tt] = make_float2(0.f, 0.f);
       if (head == 0 && row_ok) {
-        const float2 b = *reinterpret_cast<const float2*>(P.layers[layer].b_proj + col0 + 8 * tt);
+        const float2 b = *reinterpret_cast<const float2*>(layer_f(P, layer) + kFOffBproj + col0 + 8 * tt);
         const float2 xo = ld_cg_f2(P.x + (size_t)row * kD + col0 + 8 * tt);
         add[tt] = make_float2(xo.x + b.x, xo.y + b.y);
       }
@@ -485,8 +492,12 @@ __device__ void proj_splitk(const Params& P, int layer, int head, int rank, int 
       for (int tt = 0; tt < 2; ++tt)
       {
         long long* yp = P.y + (size_t)row * kD + col0 + 8 * tt;
-        red_add_s64(yp, to_fixed((hh ? acc[tt][2] : acc[tt][0]) + add[tt].x));
-        red_add_s64(yp + 1, to_fixed((hh ? acc[tt][3] : acc[tt][1]) + add[tt].y));
+        if (P.dbg_flags & 4) {   // timing experiment only (wrong results): plain stores instead of atomics
+          *reinterpret_cast<longlong2*>(yp) = make_longlong2(to_fixed(acc[tt][0]), to_fixed(acc[tt][1]));
+        } else {
+          red_add_s64(yp, to_fixed((hh ? acc[tt][2] : acc[tt][0]) + add[tt].x));
+          red_add_s64(yp + 1, to_fixed((hh ? acc[tt][3] : acc[tt][1]) + add[tt].y));
+        }
       }
     }
   }
@@ -513,7 +524,7 @@ __device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pi
   float2 bias = make_float2(0.f, 0.f);
   if (owner) {
     old = ld_cg_ll2(P.y + (size_t)erow * kD + col);
-    bias = *reinterpret_cast<const float2*>(P.layers[layer].b_proj2 + col);
+    bias = *reinterpret_cast<const float2*>(layer_f(P, layer) + kFOffBproj2 + col);
   }
   float acc[2][4];
 #pragma unroll
@@ -636,15 +647,15 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       if (layer == 0) build_rinfo(P, row_lo + 2 * rank, sm);
       ins.op = OP_LN_QKV; ins.flags = 0;
       if (P.dbg_flags & 1) {
-        ln_rows_to_smem<false>(P, ins, sm.a_rm, P.x, P.layers[layer].ln1_g, P.layers[layer].ln1_b, nullptr, nullptr, 1);
+        ln_rows_to_smem<false>(P, ins, sm.a_rm, P.x, layer_f(P, layer) + kFOffLn1g, layer_f(P, layer) + kFOffLn1b, nullptr, nullptr, 1);
         consumer_sync();
       } else {
-        ln_cluster<false>(P, ins, sm, P.x, P.layers[layer].ln1_g, P.layers[layer].ln1_b, nullptr, nullptr, rank, head, layer + 1);
+        ln_cluster<false>(P, ins, sm, P.x, layer_f(P, layer) + kFOffLn1g, layer_f(P, layer) + kFOffLn1b, nullptr, nullptr, rank, head, layer + 1);
         cluster_barrier();
       }
       prof_mark(P, c, 1);
       {
-        const float* bias = P.layers[layer].b_qkv;
+        const float* bias = layer_f(P, layer) + kFOffBqkv;
         const int* ri = rinfo_ptr(sm);
         const int t0 = head * 8 + 2 * rank;
         gemm16<6, true>(P, sm, pipe, fd, 6, row_lo, bias, [&](int i) { return t0 + (i >> 1) * (kD / 8) + (i & 1); },
@@ -674,15 +685,15 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       prof_mark(P, c, 200 + OP_LN_FC);
       ins.op = OP_LN_FC; ins.flags = F_FIXED_SRC;
       if (P.dbg_flags & 1) {
-        ln_rows_to_smem<false>(P, ins, sm.a_rm, P.x, P.layers[layer].ln2_g, P.layers[layer].ln2_b, nullptr, nullptr, 1);
+        ln_rows_to_smem<false>(P, ins, sm.a_rm, P.x, layer_f(P, layer) + kFOffLn2g, layer_f(P, layer) + kFOffLn2b, nullptr, nullptr, 1);
         consumer_sync();
       } else {
-        ln_cluster<false>(P, ins, sm, P.x, P.layers[layer].ln2_g, P.layers[layer].ln2_b, nullptr, nullptr, rank, head, -1);
+        ln_cluster<false>(P, ins, sm, P.x, layer_f(P, layer) + kFOffLn2g, layer_f(P, layer) + kFOffLn2b, nullptr, nullptr, rank, head, -1);
         cluster_barrier();
       }
       prof_mark(P, c, 1);
       {
-        const float* bias = P.layers[layer].b_fc;
+        const float* bias = layer_f(P, layer) + kFOffBfc;
         const int t0 = blockIdx.x * 4;
         gemm16<4, false>(P, sm, pipe, fd, 4, 0, bias, [&](int i) { return t0 + i; }, [&](int row, int col, float v0, float v1) {
           if (row >= n) return;

@@ -59,6 +59,13 @@ struct Params {
   int decode_mode;       // 1: rows are sequences (private pages); 0: rows are prompt positions
   // weights
   const LayerDev* layers;
+  // the same pointers as arithmetic (no dependent pointer load on the critical path): layer l's packed weights start at
+  // warena + l * w_layer_u4 (c_attn | attn.c_proj | c_fc | mlp.c_proj | split-K attn.c_proj), its fp32 parameters at
+  // fparams + l * fp_layer (ln_1 g,b | ln_2 g,b | b_attn | b_proj | b_fc | b_proj2)   (tts_ar.cu create_impl)
+  const uint4* warena;
+  const float* fparams;
+  long long w_layer_u4;
+  int fp_layer;
   const uint4* w_head;
   const float *b_head, *lnf_g, *lnf_b, *fn_g, *fn_b;
   const float *mel_emb, *mel_pos;
@@ -125,6 +132,20 @@ struct Params {
   int dbg_flags;         // bring-up A/B switches (TTS_AR_DBG): bit 0 = per-CTA LayerNorm instead of the cluster-cooperative one
   int skip_last_model;   // generate(): the model is not run after the last sampled token
 };
+
+constexpr int kU4PerChunkP = kChunkBytes / 16;
+struct LayerPtr {          // layer-l views computed from Params (device side)
+  const uint4 *w_qkv, *w_proj, *w_fc, *w_proj2, *w_projk;
+  const float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *b_qkv, *b_proj, *b_fc, *b_proj2;
+};
+TTS_HD const uint4* layer_w(const Params& P, int l) { return P.warena + (long long)l * P.w_layer_u4; }
+TTS_HD const float* layer_f(const Params& P, int l) { return P.fparams + (long long)l * P.fp_layer; }
+constexpr long long kOffProj = (long long)(kD3 / 8) * kU4PerChunkP;
+constexpr long long kOffFc = kOffProj + (long long)(kD / 8) * kU4PerChunkP;
+constexpr long long kOffProj2 = kOffFc + (long long)(kD4 / 8) * kU4PerChunkP;
+constexpr long long kOffProjk = kOffProj2 + (long long)(kD / 8) * 4 * kU4PerChunkP;
+constexpr int kFOffLn1g = 0, kFOffLn1b = kD, kFOffLn2g = 2 * kD, kFOffLn2b = 3 * kD, kFOffBqkv = 4 * kD,
+              kFOffBproj = 4 * kD + kD3, kFOffBfc = 5 * kD + kD3, kFOffBproj2 = 5 * kD + kD3 + kD4;
 
 // dynamic shared memory layout of the interpreter kernel
 constexpr int kSmemCtrlBytes = 1024;

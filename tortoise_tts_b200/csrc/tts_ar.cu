@@ -76,10 +76,12 @@ static int create_impl(TtsArHandle* h) {
   const size_t chunks_per_layer = kD3 / 8 + kD / 8 + kD4 / 8 + (kD / 8) * 4 + kProjkChunks;
   const size_t u4_per_chunk = kChunkBytes / 16;
   DALLOC(h, h->d_warena, (L * chunks_per_layer + h->v_tiles) * u4_per_chunk);
+  h->w_layer_u4 = (long long)(chunks_per_layer * u4_per_chunk);
   h->d_w_head = h->d_warena + L * chunks_per_layer * u4_per_chunk;
   // fp32 parameter arena: per layer ln1 g/b, ln2 g/b (4*1024), b_qkv 3072, b_proj 1024, b_fc 4096, b_proj2 1024
   const size_t fp_per_layer = 4 * kD + kD3 + kD + kD4 + kD;
   DALLOC(h, h->d_fparams, L * fp_per_layer + 4 * kD + h->v_stride);
+  h->fp_layer = (int)fp_per_layer;
   DALLOC(h, h->d_layers, L);
   h->layers_host.resize(L);
   for (size_t i = 0; i < L; ++i) {

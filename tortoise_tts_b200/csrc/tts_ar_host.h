@@ -29,6 +29,8 @@ struct TtsArHandle {
   std::vector<tts::LayerDev> layers_host;
   tts::LayerDev* d_layers = nullptr;
   uint4* d_warena = nullptr;
+  long long w_layer_u4 = 0;         // uint4 per layer in the packed-weight arena
+  int fp_layer = 0;                 // floats per layer in the fp32 parameter arena
   float* d_fparams = nullptr;       // LN gains/biases, linear biases (fp32)
   uint4* d_w_head = nullptr;
   float *d_b_head = nullptr, *d_lnf_g = nullptr, *d_lnf_b = nullptr, *d_fn_g = nullptr, *d_fn_b = nullptr;

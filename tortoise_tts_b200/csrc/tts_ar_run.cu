@@ -18,6 +18,7 @@ void fill_common_params(TtsArHandle* h, Params& P) {
   P.v_tiles = h->v_tiles;
   P.v_stride = h->v_stride;
   P.layers = h->d_layers;
+  P.warena = h->d_warena; P.fparams = h->d_fparams; P.w_layer_u4 = h->w_layer_u4; P.fp_layer = h->fp_layer;
   P.w_head = h->d_w_head;
   P.b_head = h->d_b_head;
   P.lnf_g = h->d_lnf_g; P.lnf_b = h->d_lnf_b; P.fn_g = h->d_fn_g; P.fn_b = h->d_fn_b;
