@@ -13,7 +13,7 @@ ends with the NCCL all-gather of the codes.
 value : tokens/s, inputs resident in HBM, CUDA events, max over ranks.
 e2e   : the same job through the host-buffer C-ABI entry (tts_ar_inference_speech_host): pinned host inputs,
         H2D + prompt pass + sample loop + D2H of the codes inside the timed region.
-roofline : the persistent decode kernel (ar_program_kernel): SURVEY.md 8(d) algorithmic bytes / its device time.
+roofline : the persistent decode kernel (ar_decode_kernel): SURVEY.md 8(d) algorithmic bytes / its device time.
 cpu_baseline : the oracle (CPU restatement of the reference path) on config C1, bounded sample, host cores.
 --impl reference : the reference's CPU implementation of the path (oracle port; the reference's own
         generate() does not run on the installed transformers) on the C2 workload, bounded sample.
@@ -292,7 +292,7 @@ def run_ours(args):
         achieved = (sum(dec_bytes) / len(dec_bytes)) / (sum(dec_ms) / len(dec_ms) * 1e-3) / 1e9
         traffic = None
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("ar_program_kernel_decode_bytes")
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("ar_decode_kernel_c2_launch_bytes")
         except Exception:
             pass
         line = {"metric": METRIC, "value": round(value, 1), "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
@@ -304,7 +304,7 @@ def run_ours(args):
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                              "frac": round(achieved / peak, 4), "traffic": traffic,
-                             "kernel": "ar_program_kernel (persistent decode loop, one launch per job)",
+                             "kernel": "ar_decode_kernel (persistent head-cluster decode loop, one launch per job)",
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s",
                              "algorithmic_bytes_per_launch": sum(dec_bytes) / len(dec_bytes),
                              "launch_ms": round(sum(dec_ms) / len(dec_ms), 3),
