@@ -30,7 +30,17 @@ print(f"N={n_cand} steps={steps}: device {s.last_device_ms:.2f} ms, prefill {s.l
 if "TTS_AR_PROF_STEP" in os.environ:
     n_instr = 1 + layers * 5 + 1
     prog = np.array([[6]] + [[o] for _ in range(layers) for o in (0, 1, 2, 3, 4)] + [[5]])   # ProgIter order
-    raw = m.debug_buffer("prof", (1024 + 4096,), dtype=torch.int64).cpu().numpy()
+    raw = m.debug_buffer("prof", (16384,), dtype=torch.int64).cpu().numpy()
+    bar = raw[8192:8192 + 128 * 8].reshape(128, 8)
+    if bar[:, 0].any():
+        for b, name in enumerate(["C->A (before ln_1)", "A->B (before ln_2)", "B->C (before mlp.c_proj)"]):
+            arr, rel = bar[:, b], bar[:, b + 3]
+            t0 = arr.min()
+            order = np.argsort(arr)
+            print(f"barrier {name}: arrivals span {(arr.max() - t0) / 1e3:.2f} us (median +{(np.median(arr) - t0) / 1e3:.2f}), "
+                  f"last arrival -> first release {(rel.min() - arr.max()) / 1e3:.2f} us, -> last release {(rel.max() - arr.max()) / 1e3:.2f} us; "
+                  f"last 4 CTAs {order[-4:].tolist()}, first 4 {order[:4].tolist()}")
+    raw = raw[:1024 + 4096]
     t = raw[: 2 * n_instr].reshape(n_instr, 2)
     marks = raw[1024:].reshape(-1, 2)
     marks = marks[marks[:, 1] > 0]

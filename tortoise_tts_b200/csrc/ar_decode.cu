@@ -36,49 +36,52 @@ __device__ __forceinline__ void cluster_barrier() {
 // those slots.  The ring is therefore always n_slots chunks (more than half a layer) ahead of the consumers, across
 // grid barriers, steps and the sampler.
 struct Feed {
-  int step, layer, idx;      // cursor in the chunk sequence (thread 0 only)
-  int passes;                // model passes of this launch
-  uint32_t slot, issued;
+  uint32_t issued;           // chunks issued so far (uniform across the feed warp)
+  uint32_t per_step, total;  // chunks per model pass / in the whole launch
   uint64_t pol;
 };
 
-__device__ __forceinline__ void feed_init(const Params& P, Feed& f) {
-  f.step = 0; f.layer = 0; f.idx = 0;
-  f.passes = P.n_steps - (P.skip_last_model ? 1 : 0);
-  f.slot = 0; f.issued = 0;
+__device__ __forceinline__ void feed_init(const Params& P, Feed& f, int hcnt) {
+  f.issued = 0;
+  f.per_step = 16u * (uint32_t)P.n_layers + (uint32_t)hcnt;
+  f.total = f.per_step * (uint32_t)(P.n_steps - (P.skip_last_model ? 1 : 0));
   f.pol = make_evict_first_policy();
 }
 
-// Issue the next n chunks (thread 0 only; the n slots at the feed cursor must be free).
+// Issue the next n (<= 32) chunks: called by the whole feed warp (warp 0), lane k issues chunk k.  The n slots must be
+// free.  (Issuing a 16 KiB bulk copy costs ~0.25-0.3 us whichever thread or warp does it: the SM ingests ~55 GB/s.)
 __device__ __forceinline__ void feed(const Params& P, Ctrl* c, uint8_t* ring, Feed& f, int n, int head, int rank, int ht0,
                                      int hcnt) {
-  for (int k = 0; k < n && f.step < f.passes; ++k) {
+  const uint32_t lane = threadIdx.x & 31;
+  const uint32_t left = f.total - f.issued;
+  const uint32_t m = min((uint32_t)n, left);
+  if (lane < m) {
+    const uint32_t p = f.issued + lane;
+    const uint32_t r = p % f.per_step;
+    const uint32_t slot = p % (uint32_t)P.n_slots;
     const uint4* src;
-    if (f.layer < P.n_layers) {
-      const uint4* L = layer_w(P, f.layer);
-      const int i = f.idx;
+    if (r < 16u * (uint32_t)P.n_layers) {
+      const uint4* L = layer_w(P, (int)(r >> 4));
+      const int i = (int)(r & 15u);
       if (i < 6) src = L + (size_t)((i >> 1) * (kD / 8) + head * 8 + 2 * rank + (i & 1)) * kU4PerChunk;
       else if (i < 8) src = L + kOffProjk + (size_t)(head * 8 + 2 * rank + (i - 6)) * kU4PerChunk;
       else if (i < 12) src = L + kOffFc + (size_t)(blockIdx.x * 4 + (i - 8)) * kU4PerChunk;
       else src = L + kOffProj2 + (size_t)(blockIdx.x * 4 + (i - 12)) * kU4PerChunk;
-      if (++f.idx == 16) { f.idx = 0; ++f.layer; }
     } else {
-      src = P.w_head + (size_t)(ht0 + f.idx) * kU4PerChunk;
-      if (++f.idx == hcnt) { f.idx = 0; f.layer = 0; ++f.step; }
+      src = P.w_head + (size_t)(ht0 + (int)(r - 16u * (uint32_t)P.n_layers)) * kU4PerChunk;
     }
-    mbar_arrive_expect_tx(&c->full[f.slot], kChunkBytes);
-    bulk_g2s(ring + (size_t)f.slot * kChunkBytes, src, kChunkBytes, &c->full[f.slot], f.pol);
-    ++f.issued;
-    if (++f.slot == (uint32_t)P.n_slots) f.slot = 0;
+    mbar_arrive_expect_tx(&c->full[slot], kChunkBytes);
+    bulk_g2s(ring + (size_t)slot * kChunkBytes, src, kChunkBytes, &c->full[slot], f.pol);
   }
+  f.issued += m;
 }
 
-// What the stages need to refill the ring: called by ALL threads right after a CTA barrier that follows the reads.
-// Refills are issued by thread 0 at the grid barriers (dec_grid_barrier), right after its arrival: the SM's L2 read
-// port (~64 B/clk) then carries the 64-128 KiB of refill while the CTA waits for the other CTAs anyway, instead of
-// competing with the latency-critical loads of the stage bodies (LayerNorm rows, biases, K/V, A fragments).
+// Refills are issued by warp 0 at the grid barriers (dec_grid_barrier), right after the CTA's arrival and at most 6
+// chunks at a time: the transfer then mostly overlaps the wait for the other CTAs instead of the latency-critical loads
+// of the stage bodies (LayerNorm rows, K/V, A fragments) on the SM's L2 read port.  (Measured alternatives: a producer
+// warp refilling as slots free up 744 us/step; refills in the LayerNorm -> GEMM window 747 us; this 684 us.)
 struct Feeder {
-  Feed f;
+  Feed f;                    // meaningful in warp 0 only
   int head, rank, ht0, hcnt;
   int pending;               // ring slots read to the end since the last refill (uniform across the CTA's threads)
 };
@@ -91,6 +94,10 @@ struct Feeder {
 //   [64 + 64j + i] prefix page table (i < 32) / private page table (i >= 32) of attention row j
 constexpr int kRinfoOffsetFloats = 7168;     // above the 24 KiB the 6-tile split-K reduction uses
 __device__ __forceinline__ int* rinfo_ptr(const Smem& sm) { return reinterpret_cast<int*>(sm.red + kRinfoOffsetFloats); }
+// attention context of this cluster's head, 16 rows x 64 dims bf16 in mma A-fragment order (2 KiB): every CTA of the
+// cluster holds a full copy, written through distributed shared memory by the CTA that merged the row
+constexpr int kCtxOffsetFloats = 7680;
+__device__ __forceinline__ uint4* ctx_smem(const Smem& sm) { return reinterpret_cast<uint4*>(sm.red + kCtxOffsetFloats); }
 
 __device__ void build_rinfo(const Params& P, int rbase, const Smem& sm) {
   int* ri = rinfo_ptr(sm);
@@ -154,7 +161,8 @@ __device__ void ln_cluster(const Params& P, const Instr& ins, const Smem& sm, co
       for (int d = 0; d < kClusterSize; ++d) st_cluster_u2(dst + (128 * j + 4 * lane) * 2, d, pk);
     }
     prof_mark(P, sm.ctrl, 23);
-  } else if (pf_layer >= 0 && pf_layer <= P.n_layers) {
+  } else {
+    if (pf_layer >= 0 && pf_layer <= P.n_layers) {
     const int t = threadIdx.x - 128;                 // 0..127
     // the small fp32 parameters (LN gains/biases, GEMM biases: one contiguous block per layer, tts_ar.cu) are
     // read once per step and do not survive 1.3 GB of streaming in L2: pull the next block in, 1/128 per CTA
@@ -167,16 +175,16 @@ __device__ void ln_cluster(const Params& P, const Instr& ins, const Smem& sm, co
         bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(P.lnf_g) + (size_t)blockIdx.x * per, per);
       }
     }
-    if (pf_layer == P.n_layers) return;
     const int* ri = rinfo_ptr(sm);
     const int j = t >> 6, i = t & 63, pg = i >> 1, kv = i & 1;
     const int len = ri[32 + j], plen = ri[34 + j];
-    if (len > 0) {
+    if (pf_layer < P.n_layers && len > 0) {
       const int* pt = ri + 64 + 64 * j;
       const __nv_bfloat16* base = P.kv + kv_row_offset(pf_layer, P.n_pages, 0, kv, head, 0);
       const size_t page_stride = (size_t)2 * kH * kPage * kHD;
       if (pg * kPage < plen) bulk_prefetch_l2(base + (size_t)pt[pg] * page_stride, kPage * kHD * 2);
       if (pg * kPage < len - plen) bulk_prefetch_l2(base + (size_t)pt[32 + pg] * page_stride, kPage * kHD * 2);
+    }
     }
   }
 }
@@ -338,7 +346,11 @@ __device__ void attn_local(const Params& P, int layer, int head, int rbase, cons
       o0 *= inv;
       o1 *= inv;
     }
-    write_ctx_pair(P, row, head * kHD + 2 * lane, o0, o1);
+    // the split-K c_proj of all 4 CTAs reads this row: push the pair into everyone's copy
+    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(ctx_smem(sm)) + afrag_elem_offset(row, 2 * lane, kHD);
+    const uint32_t pk = pack_bf16x2(o0, o1);
+#pragma unroll
+    for (int d = 0; d < kClusterSize; ++d) st_cluster_u32(dst, d, pk);
   }
   prof_mark(P, sm.ctrl, 13);
 }
@@ -349,7 +361,7 @@ __device__ void attn_local(const Params& P, int layer, int head, int rbase, cons
 // HALF: only rows [row_lo, row_lo + 8) are produced (c_attn: the other half belongs to the sibling cluster).
 // epi(row, col, v0, v1) receives the fp32 sums of columns col, col+1 (col = 8 * tile_of(i) + even offset).
 // `bias` (indexed by output column) is fetched before the mma loop for the (at most two) pairs a thread finishes.
-template <int NT, bool HALF, typename TileFn, typename Epi>
+template <int NT, bool HALF, bool TAILSYNC, typename TileFn, typename Epi>
 __device__ __forceinline__ void gemm16(const Params& P, const Smem& sm, Pipe& pipe, Feeder& fd, int cnt, int row_lo, const float* bias,
                                        TileFn tile_of, Epi epi) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -438,7 +450,7 @@ __device__ __forceinline__ void gemm16(const Params& P, const Smem& sm, Pipe& pi
     epi((ln >> 2) + 8 * hh, tile_of(t) * 8 + 2 * (ln & 3), s0 + bpre[q].x, s1 + bpre[q].y);
   }
   prof_mark(P, c, 3);
-  consumer_sync();
+  if (TAILSYNC) consumer_sync();   // else: the caller's next cluster / grid barrier protects the reduction buffer
 }
 
 // ---- split-K attn.c_proj: y[rows, 256r .. 256r+256) += ctx[rows, 64h .. 64h+64) . W[64h .. 64h+64, 256r ..] ------
@@ -447,10 +459,9 @@ __device__ __forceinline__ void gemm16(const Params& P, const Smem& sm, Pipe& pi
 __device__ void proj_splitk(const Params& P, int layer, int head, int rank, int row_lo, const Smem& sm, Pipe& pipe) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   Ctrl* c = sm.ctrl;
-  const uint4* a_gl = reinterpret_cast<const uint4*>(P.ctx) + (size_t)(head * 4) * 32 + lane;   // m-tile 0, kb = 4h + j
-  uint4 a[4];
+  uint4 a[4];                                      // A fragments of the head's context: kb = 0..3 of the local copy
 #pragma unroll
-  for (int j = 0; j < 4; ++j) a[j] = ld_cg_u4(a_gl + j * 32);
+  for (int j = 0; j < 4; ++j) a[j] = ctx_smem(sm)[j * 32 + lane];
   const int g = lane >> 2, t = lane & 3;
   const int hh = row_lo >> 3;                      // which half of the C fragment is ours: regs 2hh, 2hh+1
   const int row = row_lo + g;
@@ -562,19 +573,29 @@ __device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pi
 }
 
 // ---- grid-wide barrier of this kernel ---------------------------------------------------------------------------------
-// Same counter protocol as ar_core.cuh grid_barrier.  Thread 0 also refills `refill_n` ring slots while it waits.
+// Same counter protocol as ar_core.cuh grid_barrier.  Warp 0 also refills ring slots right after the arrival.
 // Acquire side: everything other CTAs write during the launch is read with ld.global.cg (L2, the coherence point)
 // and those loads are issued after the poll load has returned the final count, so no gpu-scope fence (and no L1
 // invalidate) is needed after the poll; TTS_AR_DBG bit 1 puts the fence back (A/B switch).
-__device__ __forceinline__ bool dec_grid_barrier(const Params& P, const Smem& sm, uint32_t& epoch, Feeder& fd, int extra) {
+__device__ __forceinline__ bool dec_grid_barrier(const Params& P, const Smem& sm, uint32_t& epoch, Feeder& fd, int extra,
+                                                 int prof_slot = -1) {
   Ctrl* c = sm.ctrl;
+  // bring-up: arrival / release time of every CTA at the three barriers of one layer (scripts/stage_prof.py)
+  const bool rec = P.prof && prof_slot >= 0 && threadIdx.x == 0;
+  if (rec) P.prof[8192 + blockIdx.x * 8 + prof_slot] = globaltimer_ns();
   consumer_sync();
   ++epoch;
-  const int refill_n = fd.pending + extra;
-  fd.pending = 0;
-  if (threadIdx.x == 0) {
-    red_release_add_u32(P.bar_counter, 1u);
+  // at most 6 chunks (96 KiB) per barrier: a larger burst is still arriving when the LayerNorm loads that follow
+  // the barrier are issued, and those then queue behind it
+  fd.pending += extra;
+  const int refill_n = min(fd.pending, 6);
+  fd.pending -= refill_n;
+  if (threadIdx.x < 32) {
+    if (threadIdx.x == 0) red_release_add_u32(P.bar_counter, 1u);
+    __syncwarp();
     if (refill_n) feed(P, c, sm.ring, fd.f, refill_n, fd.head, fd.rank, fd.ht0, fd.hcnt);
+  }
+  if (threadIdx.x == 0) {
     const uint32_t target = epoch * (uint32_t)P.G;
     const long long t0 = clock64();
     uint32_t spins = 0;
@@ -590,6 +611,7 @@ __device__ __forceinline__ bool dec_grid_barrier(const Params& P, const Smem& sm
     if (P.dbg_flags & 2) fence_acq_rel_gpu();
   }
   consumer_sync();
+  if (rec) P.prof[8192 + blockIdx.x * 8 + prof_slot + 3] = globaltimer_ns();
   return c->abort_flag == 0;
 }
 
@@ -610,10 +632,12 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
     c->ibuf[0] = 0;
     c->ibuf[1] = 0;
     fence_mbar_init();
-    feed_init(P, fd.f);
-    feed(P, c, sm.ring, fd.f, P.n_slots, head, rank, fd.ht0, fd.hcnt);
   }
   __syncthreads();
+  if (threadIdx.x < 32) {
+    feed_init(P, fd.f, fd.hcnt);
+    feed(P, c, sm.ring, fd.f, P.n_slots, head, rank, fd.ht0, fd.hcnt);
+  }
   cluster_sync_all();          // all CTAs of the cluster are running before anyone writes into a peer's shared memory
 
   Pipe pipe;
@@ -640,25 +664,21 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       ins.layer = layer;
       // ---- phase A: ln_1 -> q,k,v of this head -> attention -> split-K c_proj -> y ----
       prof_mark(P, c, 100 + OP_LN_QKV);
-      alive = dec_grid_barrier(P, sm, epoch, fd, 0);
+      const int pslot = (step == P.prof_step && layer == 3) ? 0 : -4;
+      alive = dec_grid_barrier(P, sm, epoch, fd, 0, pslot);
       if (!alive) break;
       prof_mark(P, c, 200 + OP_LN_QKV);
       if (layer == 0 && ld_cg_i(P.n_active) == 0) { alive = false; break; }
       if (layer == 0) build_rinfo(P, row_lo + 2 * rank, sm);
       ins.op = OP_LN_QKV; ins.flags = 0;
-      if (P.dbg_flags & 1) {
-        ln_rows_to_smem<false>(P, ins, sm.a_rm, P.x, layer_f(P, layer) + kFOffLn1g, layer_f(P, layer) + kFOffLn1b, nullptr, nullptr, 1);
-        consumer_sync();
-      } else {
-        ln_cluster<false>(P, ins, sm, P.x, layer_f(P, layer) + kFOffLn1g, layer_f(P, layer) + kFOffLn1b, nullptr, nullptr, rank, head, layer + 1);
-        cluster_barrier();
-      }
+      ln_cluster<false>(P, ins, sm, P.x, layer_f(P, layer) + kFOffLn1g, layer_f(P, layer) + kFOffLn1b, nullptr, nullptr, rank, head, layer + 1);
+      cluster_barrier();
       prof_mark(P, c, 1);
       {
         const float* bias = layer_f(P, layer) + kFOffBqkv;
         const int* ri = rinfo_ptr(sm);
         const int t0 = head * 8 + 2 * rank;
-        gemm16<6, true>(P, sm, pipe, fd, 6, row_lo, bias, [&](int i) { return t0 + (i >> 1) * (kD / 8) + (i & 1); },
+        gemm16<6, true, false>(P, sm, pipe, fd, 6, row_lo, bias, [&](int i) { return t0 + (i >> 1) * (kD / 8) + (i & 1); },
                         [&](int row, int col, float v0, float v1) {
                           if (row >= n) return;
                           const int part = col >> 10, cc = col & (kD - 1);
@@ -680,22 +700,17 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       proj_splitk(P, layer, head, rank, row_lo, sm, pipe);
       // ---- phase B: ln_2 -> c_fc -> gelu_new ----
       prof_mark(P, c, 100 + OP_LN_FC);
-      alive = dec_grid_barrier(P, sm, epoch, fd, 2);     // + the two split-K c_proj slots
+      alive = dec_grid_barrier(P, sm, epoch, fd, 2, pslot + 1);     // + the two split-K c_proj slots
       if (!alive) break;
       prof_mark(P, c, 200 + OP_LN_FC);
       ins.op = OP_LN_FC; ins.flags = F_FIXED_SRC;
-      if (P.dbg_flags & 1) {
-        ln_rows_to_smem<false>(P, ins, sm.a_rm, P.x, layer_f(P, layer) + kFOffLn2g, layer_f(P, layer) + kFOffLn2b, nullptr, nullptr, 1);
-        consumer_sync();
-      } else {
-        ln_cluster<false>(P, ins, sm, P.x, layer_f(P, layer) + kFOffLn2g, layer_f(P, layer) + kFOffLn2b, nullptr, nullptr, rank, head, -1);
-        cluster_barrier();
-      }
+      ln_cluster<false>(P, ins, sm, P.x, layer_f(P, layer) + kFOffLn2g, layer_f(P, layer) + kFOffLn2b, nullptr, nullptr, rank, head, -1);
+      cluster_barrier();
       prof_mark(P, c, 1);
       {
         const float* bias = layer_f(P, layer) + kFOffBfc;
         const int t0 = blockIdx.x * 4;
-        gemm16<4, false>(P, sm, pipe, fd, 4, 0, bias, [&](int i) { return t0 + i; }, [&](int row, int col, float v0, float v1) {
+        gemm16<4, false, false>(P, sm, pipe, fd, 4, 0, bias, [&](int i) { return t0 + i; }, [&](int row, int col, float v0, float v1) {
           if (row >= n) return;
           const float h0 = gelu_new(v0), h1 = gelu_new(v1);
           *reinterpret_cast<uint32_t*>(P.hbuf + afrag_elem_offset(row, col, kD4)) = pack_bf16x2(h0, h1);
@@ -703,7 +718,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       }
       // ---- phase C: mlp.c_proj, x = y + . ----
       prof_mark(P, c, 100 + OP_PROJ2);
-      alive = dec_grid_barrier(P, sm, epoch, fd, 0);
+      alive = dec_grid_barrier(P, sm, epoch, fd, 0, pslot + 2);
       if (!alive) break;
       prof_mark(P, c, 200 + OP_PROJ2);
       proj2_stage(P, layer, sm, pipe, fd);
@@ -719,7 +734,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
     cluster_barrier();
     for (int tb = 0; tb < hcnt; tb += 6) {
       const int t0 = ht0 + tb;
-      gemm16<6, false>(P, sm, pipe, fd, min(6, hcnt - tb), 0, P.b_head, [&](int i) { return t0 + i; },
+      gemm16<6, false, true>(P, sm, pipe, fd, min(6, hcnt - tb), 0, P.b_head, [&](int i) { return t0 + i; },
                        [&](int row, int col, float v0, float v1) {
                          if (row >= n) return;
                          float* lp = P.logits + (size_t)row * P.v_stride + col;     // b_head is zero-padded to v_stride
@@ -730,8 +745,8 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
     if (c->abort_flag) alive = false;
   }
   consumer_sync();
+  if (threadIdx.x == 0 && blockIdx.x == 0) *P.steps_done = steps_done;
   if (threadIdx.x == 0) {
-    if (blockIdx.x == 0) *P.steps_done = steps_done;
     // never leave the kernel with bulk copies still landing in this CTA's shared memory
     for (uint32_t k = pipe.ci; k < fd.f.issued; ++k)
       if (!mbar_wait(&c->full[k % P.n_slots], (k / P.n_slots) & 1, &c->abort_flag)) break;

@@ -126,6 +126,14 @@ __device__ __forceinline__ void st_cluster_u2(void* local_ptr, uint32_t rank, ui
       "r"(rank), "r"(v.x), "r"(v.y)
       : "memory");
 }
+__device__ __forceinline__ void st_cluster_u32(void* local_ptr, uint32_t rank, uint32_t v) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "st.shared::cluster.u32 [ra], %2;\n\t}" ::"r"(smem_u32(local_ptr)),
+      "r"(rank), "r"(v)
+      : "memory");
+}
 // fire-and-forget bulk prefetch of `bytes` (multiple of 16) of global memory into L2
 __device__ __forceinline__ void bulk_prefetch_l2(const void* p, uint32_t bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");

@@ -138,7 +138,7 @@ static int create_impl(TtsArHandle* h) {
   DALLOC(h, h->d_steps_done, 4);
   if (const char* e = getenv("TTS_AR_PROF_STEP")) {   // bring-up only: per-stage timestamps of one decode step
     h->prof_step = atoi(e);
-    DALLOC(h, h->d_prof, 1024 + 4096);
+    DALLOC(h, h->d_prof, 16384);
   }
   DALLOC(h, h->d_in_latent, (size_t)c.max_utts * kD);
   DALLOC(h, h->d_in_text, (size_t)c.max_utts * std::max(c.max_text_len, 1));
