@@ -66,7 +66,7 @@ __device__ __forceinline__ void feed(const Params& P, Ctrl* c, uint8_t* ring, Fe
       if (i < 6) src = L + (size_t)((i >> 1) * (kD / 8) + head * 8 + 2 * rank + (i & 1)) * kU4PerChunk;
       else if (i < 8) src = L + kOffProjk + (size_t)(head * 8 + 2 * rank + (i - 6)) * kU4PerChunk;
       else if (i < 12) src = L + kOffFc + (size_t)(blockIdx.x * 4 + (i - 8)) * kU4PerChunk;
-      else src = L + kOffProj2 + (size_t)(blockIdx.x * 4 + (i - 12)) * kU4PerChunk;
+      else src = L + kOffProj2 + (size_t)(((blockIdx.x & ~3) + (i - 12)) * 4 + rank) * kU4PerChunk;   // tile 4c+i, K quarter = rank
     } else {
       src = P.w_head + (size_t)(ht0 + (int)(r - 16u * (uint32_t)P.n_layers)) * kU4PerChunk;
     }
@@ -514,21 +514,21 @@ __device__ void proj_splitk(const Params& P, int layer, int head, int rank, int 
   }
 }
 
-// ---- mlp.c_proj: x[:, 8c .. 8c+8) = y + h . W[:, 8c ..] + bias ; y handed back zeroed -----------------------------------
-// One n8-tile per CTA, K = 4096 = 4 streamed chunks; warp w owns k16-blocks 8w..8w+7 of every chunk.  All 32 A
-// fragments of the warp (h is bf16 in mma A-fragment order in global memory, L2-resident) are requested before the
-// first mma, so the stage costs one L2 round trip instead of one per chunk.
-__device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pipe, Feeder& fd) {
+// ---- mlp.c_proj: x = y + h . W + bias ; y handed back zeroed ------------------------------------------------------------
+// A cluster owns 4 n8-tiles (32 output columns); CTA rank r multiplies the K range [1024r, 1024r+1024) of h with the 4
+// tiles (4 streamed chunks), so it reads only its quarter of h (32 KiB of bf16 A fragments from L2 instead of 128 KiB:
+// the SM's ~55 GB/s L2 read port is what this stage waits for).  The four K-partials of a tile are sent to the tile's
+// owner (rank t owns tile t) through distributed shared memory and summed there in rank order (deterministic).
+constexpr int kXredOffsetFloats = 6144;     // [4 source ranks][64 pairs] float2, above the 16 KiB in-CTA reduction
+__device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pipe, Feeder& fd, int rank) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   Ctrl* c = sm.ctrl;
-  const uint4* a_gl = reinterpret_cast<const uint4*>(P.hbuf) + (size_t)(w * 8) * 32 + lane;   // m-tile 0
-  uint4 a[32];
+  const uint4* a_gl = reinterpret_cast<const uint4*>(P.hbuf) + (size_t)(rank * kKbPerChunk + w * 8) * 32 + lane;   // m-tile 0
+  uint4 a[8];
 #pragma unroll
-  for (int q = 0; q < 4; ++q)
-#pragma unroll
-    for (int i = 0; i < 8; ++i) a[q * 8 + i] = ld_cg_u4(a_gl + (size_t)(q * kKbPerChunk + i) * 32);
-  // epilogue operands of the threads that own an output pair (64 pairs: 16 rows x 4 column pairs)
-  const int col = blockIdx.x * 8 + 2 * ((threadIdx.x >> 1) & 3);
+  for (int i = 0; i < 8; ++i) a[i] = ld_cg_u4(a_gl + (size_t)i * 32);
+  // epilogue operands of the threads that own an output pair of tile `rank` (64 pairs: 16 rows x 4 column pairs)
+  const int col = ((blockIdx.x & ~3) + rank) * 8 + 2 * ((threadIdx.x >> 1) & 3);
   const int erow = (threadIdx.x >> 3) + 8 * (threadIdx.x & 1);
   const bool owner = threadIdx.x < 64 && erow < P.n_rows;
   longlong2 old = make_longlong2(0ll, 0ll);
@@ -537,32 +537,66 @@ __device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pi
     old = ld_cg_ll2(P.y + (size_t)erow * kD + col);
     bias = *reinterpret_cast<const float2*>(layer_f(P, layer) + kFOffBproj2 + col);
   }
-  float acc[2][4];
+  float acc[4][2][4];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) acc[0][j] = acc[1][j] = 0.f;
+  for (int t = 0; t < 4; ++t)
 #pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    mbar_wait(&c->full[pipe.slot], pipe.phase, &c->abort_flag);
-    const uint4* bsm = reinterpret_cast<const uint4*>(sm.ring + (size_t)pipe.slot * kChunkBytes) + (w * 4) * 32 + lane;
+    for (int j = 0; j < 4; ++j) acc[t][0][j] = acc[t][1][j] = 0.f;
+  Pipe p2 = pipe;
+  bool ok = true;
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    ok &= mbar_try_wait(&c->full[p2.slot], p2.phase);
+    p2.advance();
+  }
+  if (!ok) {
+    p2 = pipe;
+    for (int t = 0; t < 4; ++t) {
+      mbar_wait(&c->full[p2.slot], p2.phase, &c->abort_flag);
+      p2.advance();
+    }
+  }
+  p2 = pipe;
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    const uint4* bsm = reinterpret_cast<const uint4*>(sm.ring + (size_t)p2.slot * kChunkBytes) + (w * 4) * 32 + lane;
 #pragma unroll
     for (int s2 = 0; s2 < 4; ++s2) {
       const uint4 b = bsm[s2 * 32];
-      mma_bf16_16816(acc[s2 & 1], a[q * 8 + 2 * s2], b.x, b.y);
-      mma_bf16_16816(acc[s2 & 1], a[q * 8 + 2 * s2 + 1], b.z, b.w);
+      mma_bf16_16816(acc[t][s2 & 1], a[2 * s2], b.x, b.y);
+      mma_bf16_16816(acc[t][s2 & 1], a[2 * s2 + 1], b.z, b.w);
     }
-    pipe.advance();
+    p2.advance();
   }
+  pipe = p2;
   float4* red4 = reinterpret_cast<float4*>(sm.red);
-  red4[w * 32 + lane] = make_float4(acc[0][0] + acc[1][0], acc[0][1] + acc[1][1], acc[0][2] + acc[1][2], acc[0][3] + acc[1][3]);
+#pragma unroll
+  for (int t = 0; t < 4; ++t)
+    red4[(w * 4 + t) * 32 + lane] = make_float4(acc[t][0][0] + acc[t][1][0], acc[t][0][1] + acc[t][1][1],
+                                                acc[t][0][2] + acc[t][1][2], acc[t][0][3] + acc[t][1][3]);
   consumer_sync();
   fd.pending += 4;
-  if (owner) {
+  {
+    // this CTA's K-partial of pair (tile t, ln, hh) -> owner CTA t
     const float2* red2 = reinterpret_cast<const float2*>(sm.red);
-    const int ln = threadIdx.x >> 1, hh = threadIdx.x & 1;
+    const int t = threadIdx.x >> 6, rem = threadIdx.x & 63, ln = rem >> 1, hh = rem & 1;
     float s0 = 0.f, s1 = 0.f;
 #pragma unroll
     for (int k = 0; k < kNW; ++k) {
-      const float2 v = red2[(k * 32 + ln) * 2 + hh];
+      const float2 v = red2[((k * 4 + t) * 32 + ln) * 2 + hh];
+      s0 += v.x;
+      s1 += v.y;
+    }
+    float2* xred = reinterpret_cast<float2*>(sm.red + kXredOffsetFloats);
+    st_cluster_u2(xred + rank * 64 + rem, (uint32_t)t, make_uint2(__float_as_uint(s0), __float_as_uint(s1)));
+  }
+  cluster_barrier();
+  if (owner) {
+    const float2* xred = reinterpret_cast<const float2*>(sm.red + kXredOffsetFloats);
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int r = 0; r < kClusterSize; ++r) {
+      const float2 v = xred[r * 64 + threadIdx.x];
       s0 += v.x;
       s1 += v.y;
     }
@@ -721,7 +755,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       alive = dec_grid_barrier(P, sm, epoch, fd, 0, pslot + 2);
       if (!alive) break;
       prof_mark(P, c, 200 + OP_PROJ2);
-      proj2_stage(P, layer, sm, pipe, fd);
+      proj2_stage(P, layer, sm, pipe, fd, rank);
       if (c->abort_flag) alive = false;
     }
     if (!alive) break;
