@@ -136,35 +136,45 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
       }
       kmin = lo;
     }
-    // ---- e = exp(score - max) over the top-k survivors ----
+    // ---- e = exp(score - max) over the top-k survivors; (key, e) of the thread's 33 tokens stay in registers ----
+    uint32_t key[kVPerThread];
+    float e[kVPerThread];
     float zl[1] = {0.f};
-#pragma unroll kSmpUnroll
-    for (int v = tid; v < V; v += kConsumerThreads) {
-      const float sv = sc[v];
-      const float e = (key_of(sv) >= kmin) ? expf(sv - smax) : 0.f;
-      ev[v] = e;
-      zl[0] += e;
+#pragma unroll
+    for (int i = 0; i < kVPerThread; ++i) {
+      const int v = tid + i * kConsumerThreads;
+      const float sv = (v < V) ? sc[v] : -INFINITY;
+      key[i] = (v < V) ? key_of(sv) : 0u;                       // 0 < key(-inf): padding never passes a probe
+      e[i] = (key[i] >= kmin) ? expf(sv - smax) : 0.f;
+      if (v < V) ev[v] = e[i];
+      zl[0] += e[i];
     }
     block_sum_k<1>(zl, rbuf + par * 32);
     par ^= 1;
     const float Z = zl[0];
     prof_mark(P, c, 32);
-    // ---- top-p: smallest T with mass{key > T} < p * Z ; keep key >= T  (4-way search) ----
+    // ---- top-p: smallest T with mass{key > T} < p * Z ; keep key >= T  (4-way search over registers) ----
     if (P.top_p < 1.0f) {
       const float lim = P.top_p * Z;
       uint32_t lo = kmin, hi = key_of(smax);        // pred(hi): mass above the max is 0 < lim
+      bool first = true;
       while (lo < hi) {
         const uint32_t q = (hi - lo) >> 2;
         uint32_t t[3];
+        if (first) {   // the nucleus edge is almost always within a few units of the maximum score: probe there first
+          t[0] = min(max(key_of(smax - 16.f), lo), hi);
+          t[1] = min(max(key_of(smax - 4.f), t[0]), hi);
+          t[2] = min(max(key_of(smax - 1.f), t[1]), hi);
+          first = false;
+        } else {
 #pragma unroll
-        for (int j = 0; j < 3; ++j) t[j] = q ? lo + q * (j + 1) - 1u : min(lo + j, hi);   // lo <= t0 <= t1 <= t2 <= hi
+          for (int j = 0; j < 3; ++j) t[j] = q ? lo + q * (j + 1) - 1u : min(lo + j, hi);   // lo <= t0 <= t1 <= t2 <= hi
+        }
         float ms[3] = {0.f, 0.f, 0.f};
-#pragma unroll kSmpUnroll
-        for (int v = tid; v < V; v += kConsumerThreads) {
-          const uint32_t k = key_of(sc[v]);
-          const float e = ev[v];
 #pragma unroll
-          for (int j = 0; j < 3; ++j) ms[j] += (k > t[j]) ? e : 0.f;
+        for (int i = 0; i < kVPerThread; ++i) {
+#pragma unroll
+          for (int j = 0; j < 3; ++j) ms[j] += (key[i] > t[j]) ? e[i] : 0.f;
         }
         block_sum_k<3>(ms, rbuf + par * 32);
         par ^= 1;
