@@ -55,6 +55,7 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
   const int V = P.V;
   const int stop = P.stop_token;
 
+  const int gen = ld_cg_i(P.gen_count + seq);       // tokens generated before this one
   const bool fin = ld_cg_i(P.finished + seq) != 0;
   if (fin) {   // finished rows keep emitting the pad (== stop) token and are not fed to the model (Q7)
     if (tid == 0) {
@@ -63,7 +64,6 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
     }
     return;
   }
-  const int gen = ld_cg_i(P.gen_count + seq);       // tokens generated before this one
   const int lrow = (P.first_step_from_prefill && step_col == 0) ? P.seq_utt[seq] : seq;
   const float* lg = P.logits + (size_t)lrow * P.v_stride;
   const uint32_t* seen = P.seen + (size_t)seq * P.seen_words;
@@ -136,18 +136,14 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
       }
       kmin = lo;
     }
-    // ---- e = exp(score - max) over the top-k survivors; (key, e) of the thread's 33 tokens stay in registers ----
-    uint32_t key[kVPerThread];
-    float e[kVPerThread];
+    // ---- e = exp(score - max) over the top-k survivors (compact loop: once-per-step code, see above) ----
     float zl[1] = {0.f};
-#pragma unroll
-    for (int i = 0; i < kVPerThread; ++i) {
-      const int v = tid + i * kConsumerThreads;
-      const float sv = (v < V) ? sc[v] : -INFINITY;
-      key[i] = (v < V) ? key_of(sv) : 0u;                       // 0 < key(-inf): padding never passes a probe
-      e[i] = (key[i] >= kmin) ? expf(sv - smax) : 0.f;
-      if (v < V) ev[v] = e[i];
-      zl[0] += e[i];
+#pragma unroll 3
+    for (int v = tid; v < V; v += kConsumerThreads) {
+      const float sv = sc[v];
+      const float ex = (key_of(sv) >= kmin) ? expf(sv - smax) : 0.f;
+      ev[v] = ex;
+      zl[0] += ex;
     }
     block_sum_k<1>(zl, rbuf + par * 32);
     par ^= 1;
@@ -155,6 +151,15 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
     prof_mark(P, c, 32);
     // ---- top-p: smallest T with mass{key > T} < p * Z ; keep key >= T  (4-way search over registers) ----
     if (P.top_p < 1.0f) {
+      // (key, e) of the thread's 33 tokens in registers: the search rounds below touch no memory
+      uint32_t key[kVPerThread];
+      float e[kVPerThread];
+#pragma unroll
+      for (int i = 0; i < kVPerThread; ++i) {
+        const int v = tid + i * kConsumerThreads;
+        key[i] = (v < V) ? key_of(sc[v]) : 0u;                    // 0 < key(-inf): padding never passes a probe
+        e[i] = (v < V) ? ev[v] : 0.f;
+      }
       const float lim = P.top_p * Z;
       uint32_t lo = kmin, hi = key_of(smax);        // pred(hi): mass above the max is 0 < lim
       bool first = true;
