@@ -456,7 +456,28 @@ __device__ __forceinline__ void gemm16(const Params& P, const Smem& sm, Pipe& pi
 // ---- split-K attn.c_proj: y[rows, 256r .. 256r+256) += ctx[rows, 64h .. 64h+64) . W[64h .. 64h+64, 256r ..] ------
 // rows = [row_lo, row_lo + 8): the half of the 16-row M tile this cluster owns (the other half of the A fragments
 // is the sibling cluster's and is ignored).  Two 16 KiB chunks of 128 columns; warp w: n8-tiles 2w, 2w+1 of each.
-__device__ void proj_splitk(const Params& P, int layer, int head, int rank, int row_lo, const Smem& sm, Pipe& pipe) {
+// Residual + bias ride on head 0's partial product: its CTAs fetch x and the bias at the start of phase A (x is final
+// since the grid barrier), so the loads are not on the path between the attention and the atomics.
+struct ProjAdd { float2 v[2][2]; };
+__device__ __forceinline__ void proj_preload(const Params& P, int layer, int head, int rank, int row_lo, ProjAdd& pa) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int row = row_lo + (lane >> 2);
+#pragma unroll
+  for (int ch = 0; ch < 2; ++ch)
+#pragma unroll
+    for (int tt = 0; tt < 2; ++tt) {
+      pa.v[ch][tt] = make_float2(0.f, 0.f);
+      if (head == 0 && row < P.n_rows) {
+        const int col = 256 * rank + 128 * ch + 16 * w + 2 * (lane & 3) + 8 * tt;
+        const float2 b = *reinterpret_cast<const float2*>(layer_f(P, layer) + kFOffBproj + col);
+        const float2 xo = ld_cg_f2(P.x + (size_t)row * kD + col);
+        pa.v[ch][tt] = make_float2(xo.x + b.x, xo.y + b.y);
+      }
+    }
+}
+
+__device__ void proj_splitk(const Params& P, int layer, int head, int rank, int row_lo, const Smem& sm, Pipe& pipe,
+                            const ProjAdd& pa) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   Ctrl* c = sm.ctrl;
   uint4 a[4];                                      // A fragments of the head's context: kb = 0..3 of the local copy
@@ -469,17 +490,7 @@ __device__ void proj_splitk(const Params& P, int layer, int head, int rank, int 
 #pragma unroll
   for (int ch = 0; ch < 2; ++ch) {
     const int col0 = 256 * rank + 128 * ch + 16 * w + 2 * t;       // tile tt adds 8
-    // residual + bias ride on head 0's partial product
-    float2 add[2];
-#pragma unroll
-    for (int tt = 0; tt < 2; ++tt) {
-      add[tt] = make_float2(0.f, 0.f);
-      if (head == 0 && row_ok) {
-        const float2 b = *reinterpret_cast<const float2*>(layer_f(P, layer) + kFOffBproj + col0 + 8 * tt);
-        const float2 xo = ld_cg_f2(P.x + (size_t)row * kD + col0 + 8 * tt);
-        add[tt] = make_float2(xo.x + b.x, xo.y + b.y);
-      }
-    }
+    const float2 add[2] = {pa.v[ch][0], pa.v[ch][1]};
     float acc[2][4];
 #pragma unroll
     for (int tt = 0; tt < 2; ++tt)
@@ -705,6 +716,8 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       if (layer == 0 && ld_cg_i(P.n_active) == 0) { alive = false; break; }
       if (layer == 0) build_rinfo(P, row_lo + 2 * rank, sm);
       ins.op = OP_LN_QKV; ins.flags = 0;
+      ProjAdd padd;
+      proj_preload(P, layer, head, rank, row_lo, padd);
       ln_cluster<false>(P, ins, sm, P.x, layer_f(P, layer) + kFOffLn1g, layer_f(P, layer) + kFOffLn1b, nullptr, nullptr, rank, head, layer + 1);
       cluster_barrier();
       prof_mark(P, c, 1);
@@ -731,7 +744,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       attn_local(P, layer, head, row_lo + 2 * rank, sm);
       cluster_barrier();
       prof_mark(P, c, 200 + OP_PROJ);
-      proj_splitk(P, layer, head, rank, row_lo, sm, pipe);
+      proj_splitk(P, layer, head, rank, row_lo, sm, pipe, padd);
       // ---- phase B: ln_2 -> c_fc -> gelu_new ----
       prof_mark(P, c, 100 + OP_LN_FC);
       alive = dec_grid_barrier(P, sm, epoch, fd, 2, pslot + 1);     // + the two split-K c_proj slots
