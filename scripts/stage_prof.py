@@ -44,7 +44,7 @@ if "TTS_AR_PROF_STEP" in os.environ:
     t = raw[: 2 * n_instr].reshape(n_instr, 2)
     marks = raw[1024:].reshape(-1, 2)
     marks = marks[marks[:, 1] > 0]
-    names = {1: "A-ready", 2: "mma-done", 3: "epi-done", 11: "attn-plan", 4: "reduce-synced", 12: "attn-partials", 13: "attn-merged", 21: "ln-loaded", 22: "ln-normalised", 23: "ln-dsmem-stored", 31: "smp-scores+max", 32: "smp-exp+Z", 33: "smp-top-p", 34: "smp-multinomial", 35: "smp-bookkeeping"}
+    names = {1: "A-ready", 2: "mma-done", 3: "epi-done", 11: "attn-plan", 4: "reduce-synced", 5: "a-frags+bias issued", 6: "chunks probed", 12: "attn-partials", 13: "attn-merged", 21: "ln-loaded", 22: "ln-normalised", 23: "ln-dsmem-stored", 31: "smp-scores+max", 32: "smp-exp+Z", 33: "smp-top-p", 34: "smp-multinomial", 35: "smp-bookkeeping"}
     names.update({100 + i: "pre-bar " + o for i, o in enumerate(OPS)})
     names.update({200 + i: "post-bar " + o for i, o in enumerate(OPS)})
     ids = marks[:, 0].tolist()

@@ -355,6 +355,26 @@ __device__ void attn_local(const Params& P, int layer, int head, int rbase, cons
   prof_mark(P, sm.ctrl, 13);
 }
 
+// Have the next cnt (<= 32) chunks of the ring landed?  Lane k probes chunk k's barrier (one try_wait for the warp
+// instead of cnt serial ones, ~0.05 us each); if one has not, every lane blocks on each in turn (watchdogged).
+// A landed chunk's bytes are in shared memory before its barrier phase flips, so any lane may read any chunk after.
+__device__ __forceinline__ void wait_chunks(Ctrl* c, const Pipe& pipe, int cnt) {
+  const int lane = threadIdx.x & 31;
+  bool mine = true;
+  if (lane < cnt) {
+    uint32_t sl = pipe.slot + (uint32_t)lane, ph = pipe.phase;
+    if (sl >= (uint32_t)pipe.n_slots) { sl -= (uint32_t)pipe.n_slots; ph ^= 1u; }
+    mine = mbar_try_wait(&c->full[sl], ph);
+  }
+  if (!__all_sync(0xffffffffu, mine)) {
+    Pipe p2 = pipe;
+    for (int t = 0; t < cnt; ++t) {
+      mbar_wait(&c->full[p2.slot], p2.phase, &c->abort_flag);
+      p2.advance();
+    }
+  }
+}
+
 // ---- 16-row GEMM over this CTA's next `cnt` (<= NT) streamed K=1024 chunks ------------------------------------------
 // A = the LayerNorm'd rows staged in sm.a_rm; warp w owns k16-blocks 8w..8w+7 of every chunk (its A fragments
 // are loaded once), the 8 partial tiles are summed through shared memory in a fixed order (deterministic).
@@ -391,23 +411,10 @@ __device__ __forceinline__ void gemm16(const Params& P, const Smem& sm, Pipe& pi
   for (int t = 0; t < NT; ++t)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[t][0][j] = acc[t][1][j] = 0.f;
-  // all chunks of the pass have normally landed long ago: probe them back to back, block only if one has not
+  prof_mark(P, c, 5);
+  wait_chunks(c, pipe, cnt);     // all chunks of the pass have normally landed long ago
   Pipe p2 = pipe;
-  bool ok = true;
-#pragma unroll
-  for (int t = 0; t < NT; ++t)
-    if (t < cnt) {
-      ok &= mbar_try_wait(&c->full[p2.slot], p2.phase);
-      p2.advance();
-    }
-  if (!ok) {
-    p2 = pipe;
-    for (int t = 0; t < cnt; ++t) {
-      mbar_wait(&c->full[p2.slot], p2.phase, &c->abort_flag);
-      p2.advance();
-    }
-  }
-  p2 = pipe;
+  prof_mark(P, c, 6);
 #pragma unroll
   for (int t = 0; t < NT; ++t)
     if (t < cnt) {
@@ -487,6 +494,7 @@ __device__ void proj_splitk(const Params& P, int layer, int head, int rank, int 
   const int hh = row_lo >> 3;                      // which half of the C fragment is ours: regs 2hh, 2hh+1
   const int row = row_lo + g;
   const bool row_ok = row < P.n_rows;
+  wait_chunks(c, pipe, 2);
 #pragma unroll
   for (int ch = 0; ch < 2; ++ch) {
     const int col0 = 256 * rank + 128 * ch + 16 * w + 2 * t;       // tile tt adds 8
@@ -496,7 +504,7 @@ __device__ void proj_splitk(const Params& P, int layer, int head, int rank, int 
     for (int tt = 0; tt < 2; ++tt)
 #pragma unroll
       for (int j = 0; j < 4; ++j) acc[tt][j] = 0.f;
-    if (mbar_wait(&c->full[pipe.slot], pipe.phase, &c->abort_flag)) {
+    {
       const uint4* bsm = reinterpret_cast<const uint4*>(sm.ring + (size_t)pipe.slot * kChunkBytes) + lane;
 #pragma unroll
       for (int tt = 0; tt < 2; ++tt) {
@@ -553,21 +561,8 @@ __device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pi
   for (int t = 0; t < 4; ++t)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[t][0][j] = acc[t][1][j] = 0.f;
+  wait_chunks(c, pipe, 4);
   Pipe p2 = pipe;
-  bool ok = true;
-#pragma unroll
-  for (int t = 0; t < 4; ++t) {
-    ok &= mbar_try_wait(&c->full[p2.slot], p2.phase);
-    p2.advance();
-  }
-  if (!ok) {
-    p2 = pipe;
-    for (int t = 0; t < 4; ++t) {
-      mbar_wait(&c->full[p2.slot], p2.phase, &c->abort_flag);
-      p2.advance();
-    }
-  }
-  p2 = pipe;
 #pragma unroll
   for (int t = 0; t < 4; ++t) {
     const uint4* bsm = reinterpret_cast<const uint4*>(sm.ring + (size_t)p2.slot * kChunkBytes) + (w * 4) * 32 + lane;
