@@ -40,6 +40,12 @@ if "TTS_AR_PROF_STEP" in os.environ:
             print(f"barrier {name}: arrivals span {(arr.max() - t0) / 1e3:.2f} us (median +{(np.median(arr) - t0) / 1e3:.2f}), "
                   f"last arrival -> first release {(rel.min() - arr.max()) / 1e3:.2f} us, -> last release {(rel.max() - arr.max()) / 1e3:.2f} us; "
                   f"last 4 CTAs {order[-4:].tolist()}, first 4 {order[:4].tolist()}")
+            if os.environ.get("BAR_DETAIL"):
+                cl = (arr - t0).reshape(32, 4)
+                print("   per-cluster arrival offset ns (max over the 4 CTAs), cluster id ascending:")
+                print("   " + " ".join(f"{int(x):4d}" for x in cl.max(axis=1)))
+                print("   per-cluster release offset ns after last arrival (max over the 4 CTAs):")
+                print("   " + " ".join(f"{int(x):4d}" for x in (rel - arr.max()).reshape(32, 4).max(axis=1)))
     raw = raw[:1024 + 4096]
     t = raw[: 2 * n_instr].reshape(n_instr, 2)
     marks = raw[1024:].reshape(-1, 2)
@@ -56,7 +62,12 @@ if "TTS_AR_PROF_STEP" in os.environ:
             print(f"HEAD: barrier wait {(marks[i4,1]-marks[i3,1])/1e3:.2f} us; step (SAMPLE pre-bar -> HEAD post-bar) {(marks[i4,1]-marks[i0,1])/1e3:.1f} us")
     if 206 in ids:
         i1 = ids.index(206)
-        for i in range(i1 + 1, min(i1 + 8, len(marks))):
+        for i in range(i1 + 1, min(i1 + 8, len(marks))):  # sampler marks
+            print(f"   {names.get(int(marks[i, 0]), marks[i, 0]):18s} +{int(marks[i, 1] - marks[i - 1, 1])}")
+    if 205 in ids:
+        i4 = ids.index(205)
+        print("marks of the HEAD phase (delta ns from previous mark):")
+        for i in range(i4, len(marks)):
             print(f"   {names.get(int(marks[i, 0]), marks[i, 0]):18s} +{int(marks[i, 1] - marks[i - 1, 1])}")
     sel = [i for i in range(len(marks)) if marks[i, 0] == 100]       # pre-barrier LN_QKV marks = layer starts
     if len(sel) > 4:

@@ -4,9 +4,13 @@
 //   reference unified_voice.py:647-649), TemperatureLogitsWarper, TopKLogitsWarper, TopPLogitsWarper in the
 //   order of the reference's _get_logits_warper (stream_generator.py:56-101), softmax + multinomial and the
 //   pad-after-stop / unfinished bookkeeping of sample_stream (stream_generator.py:1160-1190).
-// Top-k / top-p thresholds come from a bisection over the monotone uint image of the fp32 scores:
-//   top-k keeps score >= (k-th largest);   top-p keeps token i iff mass{score > score_i} < p
-// which is HF's "ascending cumsum <= 1-p -> remove" rule (tests/test_oracle_golden.py proves the identity).
+// Top-k / top-p thresholds come from ONE search routine over the monotone uint image ("key") of the fp32 scores:
+//   keep key >= T,  T = smallest key with  weight{key > T} < limit
+//   top-k: weight = 1, limit = k  (T = k-th largest score, ties kept);
+//   top-p: weight = exp(score - max), limit = p * Z  (token i is kept iff mass{score > score_i} < p, which is HF's
+//   "ascending cumsum <= 1-p -> remove" rule; tests/test_oracle_golden.py proves the identity).
+// Each round cuts the score interval in four with three probes and also counts the tokens left inside; once there
+// are <= 32 the tokens themselves are gathered and a warp-wide sort + prefix sum ends the search.
 // The multinomial is an inverse CDF in vocabulary order driven by Philox4x32-10 (oracle/philox.py).
 #pragma once
 #include "ar_core.cuh"
@@ -16,6 +20,37 @@ namespace tts {
 constexpr int kVPerThread = (8448 + kConsumerThreads - 1) / kConsumerThreads;   // covers n_mel_codes <= 8448
 
 __device__ __forceinline__ uint32_t key_of(float v) { return float_key(__float_as_uint(v)); }
+
+// Sorts one 64-bit item per lane in descending order across the warp (bitonic, shuffles only).
+__device__ __forceinline__ unsigned long long warp_sort_desc(unsigned long long v) {
+  const int lane = threadIdx.x & 31;
+#pragma unroll 1
+  for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll 1
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      const unsigned long long o = __shfl_xor_sync(0xffffffffu, v, j);
+      const bool keep_max = ((lane & j) == 0) == ((lane & k) == 0);
+      v = keep_max ? (v > o ? v : o) : (v < o ? v : o);
+    }
+  }
+  return v;
+}
+
+__device__ __forceinline__ float key_to_float(uint32_t k) {
+  return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+// Block maximum and minimum with one pair of barriers.
+__device__ __forceinline__ void block_maxmin(float& mx, float& mn, float* scratch) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  mx = warp_max(mx);
+  mn = -warp_max(-mn);
+  consumer_sync();
+  if (lane == 0) { scratch[w] = mx; scratch[kNW + w] = mn; }
+  consumer_sync();
+  mx = warp_max((lane < kNW) ? scratch[lane] : -INFINITY);
+  mn = -warp_max((lane < kNW) ? -scratch[kNW + lane] : -INFINITY);
+}
 
 // Block reduction of K floats per thread with ONE bar.sync: per-warp shuffle trees, lane 0 parks the K warp sums in
 // `buf` ([kNW][K] floats; the caller alternates two buffers between consecutive calls so no second barrier is needed
@@ -50,7 +85,10 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
   float* sc = reinterpret_cast<float*>(sm.a_rm);
   float* ev = sm.red;
   float* scratch = c->scratch;
-  float* rbuf = ev + (8448 - 64);                    // 2 x [kNW][4] floats above the V exps (V <= 8256, tts_ar_create)
+  float* rbuf = ev + 8256;                           // 2 x [kNW][6] words above the V exps (V <= 8256, tts_ar_create)
+  unsigned long long* slist = reinterpret_cast<unsigned long long*>(ev + 8352);   // 32 gathered (key, weight) candidates
+  int* scnt = reinterpret_cast<int*>(ev + 8416);
+  if (threadIdx.x == 0) *scnt = 0;                   // ordered before the first gather by the reductions' barriers
   const int tid = threadIdx.x;
   const int V = P.V;
   const int stop = P.stop_token;
@@ -70,28 +108,27 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
   const float pen = P.rep_penalty;
   const bool use_temp = P.do_sample && P.temperature != 1.0f;
 
-  // scores = processors(logits): repetition penalty, then (sampling only) temperature
-  float lmax = -INFINITY;
+  // scores = processors(logits): repetition penalty, then (sampling only) temperature; kept as keys in sk[]
+  // The row is copied L2 -> shared memory asynchronously (one round trip for the whole row), then transformed in
+  // place: thread t owns tokens t, t+256, ... from here on.
+  uint32_t* sk = reinterpret_cast<uint32_t*>(sc);
 #pragma unroll 1
-  for (int i0 = 0; i0 < kVPerThread; i0 += kSmpUnroll) {
-    float s[kSmpUnroll];
-#pragma unroll
-    for (int i = 0; i < kSmpUnroll; ++i) {
-      const int v = tid + (i0 + i) * kConsumerThreads;
-      s[i] = (v < V) ? ld_cg_f(lg + v) : -INFINITY;
-    }
-#pragma unroll
-    for (int i = 0; i < kSmpUnroll; ++i) {
-      const int v = tid + (i0 + i) * kConsumerThreads;
-      if (v < V) {
-        if (pen != 1.0f && ((__ldcg(seen + (v >> 5)) >> (v & 31)) & 1u)) s[i] = (s[i] < 0.f) ? s[i] * pen : s[i] / pen;
-        if (use_temp) s[i] = s[i] / P.temperature;
-        sc[v] = s[i];
-        lmax = fmaxf(lmax, s[i]);
-      }
-    }
+  for (int v = 4 * tid; v + 3 < P.v_stride; v += 4 * kConsumerThreads) cp_async_cg16(sc + v, lg + v);   // v_stride <= 8256
+  cp_async_wait_all();
+  consumer_sync();
+  float lmax = -INFINITY, lmin = INFINITY;
+#pragma unroll 3
+  for (int v = tid; v < V; v += kConsumerThreads) {
+    float s = sc[v];
+    if (pen != 1.0f && ((__ldcg(seen + (v >> 5)) >> (v & 31)) & 1u)) s = (s < 0.f) ? s * pen : s / pen;
+    if (use_temp) s = s / P.temperature;
+    sk[v] = key_of(s);
+    lmax = fmaxf(lmax, s);
+    lmin = fminf(lmin, s);
   }
-  const float smax = block_max(lmax, scratch);   // also orders the sc[] writes before the reads below
+  block_maxmin(lmax, lmin, scratch);               // also orders the sk[] writes before the reads below
+  const float smax = lmax, smin = lmin;
+  const uint32_t kmax = key_of(smax);
   prof_mark(P, c, 31);
 
   int token;
@@ -100,7 +137,7 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
     int best = 0x7fffffff;
 #pragma unroll kSmpUnroll
     for (int v = tid; v < V; v += kConsumerThreads)
-      if (sc[v] == smax) best = min(best, v);
+      if (sk[v] == kmax) best = min(best, v);
     best = __reduce_min_sync(0xffffffffu, best);
     consumer_sync();
     if ((tid & 31) == 0) reinterpret_cast<int*>(scratch)[tid >> 5] = best;
@@ -110,86 +147,139 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
   } else {
     uint32_t kmin = key_of(-INFINITY);             // keep key >= kmin
     int par = 0;
-    // ---- top-k: largest T with #{key >= T} >= k  (4-way search: 3 probes per round) ----
-    if (P.top_k > 0 && P.top_k < V) {
-      uint32_t lo = key_of(-INFINITY), hi = key_of(smax);   // count(lo) = V >= k; answer in [lo, hi]
-      const float kf = (float)P.top_k;                      // counts <= 8448 are exact in fp32
-      while (lo < hi) {
-        const uint32_t q = (hi - lo) >> 2;
-        uint32_t t[3];
-#pragma unroll
-        for (int j = 0; j < 3; ++j) t[j] = q ? lo + q * (j + 1) : min(lo + 1u + j, hi);   // lo < t0 <= t1 <= t2 <= hi
-        float cnt[3] = {0.f, 0.f, 0.f};
-#pragma unroll kSmpUnroll
-        for (int v = tid; v < V; v += kConsumerThreads) {
-          const uint32_t k = key_of(sc[v]);
-#pragma unroll
-          for (int j = 0; j < 3; ++j) cnt[j] += (k >= t[j]) ? 1.f : 0.f;
-        }
-        block_sum_k<3>(cnt, rbuf + par * 32);
-        par ^= 1;
-        // pred(T) = count(T) >= k is true..true false..false in T; answer = largest T with pred
-        if (cnt[2] >= kf) lo = t[2];
-        else if (cnt[1] >= kf) { lo = t[1]; hi = t[2] - 1u; }
-        else if (cnt[0] >= kf) { lo = t[0]; hi = t[1] - 1u; }
-        else hi = t[0] - 1u;
-      }
-      kmin = lo;
-    }
-    // ---- e = exp(score - max) over the top-k survivors (compact loop: once-per-step code, see above) ----
-    float zl[1] = {0.f};
+    float Z = 0.f;
+    int n_keep = V;                                 // #{key >= kmin}
+    // pass 0 = top-k, pass 1 = softmax numerators + top-p.  One copy of the search code (the sampler runs once per
+    // step, so every instruction of it is an instruction-cache miss: loops are kept rolled on purpose).
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+      const bool ones = pass == 0;
+      float lim;
+      if (ones) {
+        if (!(P.top_k > 0 && P.top_k < V)) continue;
+        lim = (float)P.top_k;                       // counts <= 8448 are exact in fp32
+      } else {
+        // e = exp(score - max) over the top-k survivors
+        float zl[2] = {0.f, 0.f};
 #pragma unroll 3
-    for (int v = tid; v < V; v += kConsumerThreads) {
-      const float sv = sc[v];
-      const float ex = (key_of(sv) >= kmin) ? expf(sv - smax) : 0.f;
-      ev[v] = ex;
-      zl[0] += ex;
-    }
-    block_sum_k<1>(zl, rbuf + par * 32);
-    par ^= 1;
-    const float Z = zl[0];
-    prof_mark(P, c, 32);
-    // ---- top-p: smallest T with mass{key > T} < p * Z ; keep key >= T  (4-way search over registers) ----
-    if (P.top_p < 1.0f) {
-      // (key, e) of the thread's 33 tokens in registers: the search rounds below touch no memory
-      uint32_t key[kVPerThread];
-      float e[kVPerThread];
-#pragma unroll
-      for (int i = 0; i < kVPerThread; ++i) {
-        const int v = tid + i * kConsumerThreads;
-        key[i] = (v < V) ? key_of(sc[v]) : 0u;                    // 0 < key(-inf): padding never passes a probe
-        e[i] = (v < V) ? ev[v] : 0.f;
+        for (int v = tid; v < V; v += kConsumerThreads) {
+          const uint32_t k = sk[v];
+          const bool keep = k >= kmin;
+          const float ex = keep ? expf(key_to_float(k) - smax) : 0.f;
+          ev[v] = ex;
+          zl[0] += ex;
+          zl[1] += keep ? 1.f : 0.f;
+        }
+        block_sum_k<2>(zl, rbuf + par * 48);
+        par ^= 1;
+        Z = zl[0];
+        n_keep = (int)zl[1];
+        prof_mark(P, c, 32);
+        if (!(P.top_p < 1.0f)) break;
+        lim = P.top_p * Z;
       }
-      const float lim = P.top_p * Z;
-      uint32_t lo = kmin, hi = key_of(smax);        // pred(hi): mass above the max is 0 < lim
+      // smallest T in [lo, hi] with weight{key > T} < lim.  pred(hi) holds: nothing lies above the maximum.
+      uint32_t lo = kmin, hi = kmax;
+      int n_lo = n_keep, n_hi = 0;                  // #{key >= lo}, #{key > hi}
+      float m_hi = 0.f;                             // weight{key > hi}
       bool first = true;
       while (lo < hi) {
-        const uint32_t q = (hi - lo) >> 2;
+        if (n_lo - n_hi <= 32) {
+          // gather the candidates (order arbitrary: sorted next), every warp finishes redundantly
+#pragma unroll 3
+          for (int v = tid; v < V; v += kConsumerThreads) {
+            const uint32_t k = sk[v];
+            if (k >= lo && k <= hi) {
+              const int p = atomicAdd(scnt, 1);
+              if (p < 32) slist[p] = ((unsigned long long)k << 32) | __float_as_uint(ones ? 1.f : ev[v]);
+            }
+          }
+          consumer_sync();
+          const int n = min(*scnt, 32);
+          const int lane = tid & 31;
+          const unsigned long long it = warp_sort_desc(lane < n ? slist[lane] : 0ull);
+          // walking down from hi, the first candidate whose inclusion lifts the weight to >= lim is the edge
+          float incl = __uint_as_float((uint32_t)it);
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const float tt = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += tt;
+          }
+          const unsigned brk = __ballot_sync(0xffffffffu, lane < n && m_hi + incl >= lim);
+          if (brk) lo = (uint32_t)(__shfl_sync(0xffffffffu, it, __ffs(brk) - 1) >> 32);
+          consumer_sync();
+          if (tid == 0) *scnt = 0;
+          break;
+        }
+        // probes lo <= t0 <= t1 <= t2 < hi: quarters of the score interval (first round: also just below the
+        // maximum, where the edge almost always is); quarters of the key interval when those degenerate
         uint32_t t[3];
-        if (first) {   // the nucleus edge is almost always within a few units of the maximum score: probe there first
-          t[0] = min(max(key_of(smax - 16.f), lo), hi);
-          t[1] = min(max(key_of(smax - 4.f), t[0]), hi);
-          t[2] = min(max(key_of(smax - 1.f), t[1]), hi);
+        {
+          const float fl = fmaxf(key_to_float(lo), smin), fh = key_to_float(hi);
+          bool ok = true;
+#pragma unroll
+          for (int j = 0; j < 3; ++j) {
+            float pj = fl + (fh - fl) * (0.25f * (j + 1));
+            if (first) pj = fmaxf(pj, smax - (j == 0 ? 16.f : j == 1 ? 4.f : 1.f));
+            t[j] = key_of(pj);
+            ok = ok && (fabsf(pj) <= 3.0e38f);
+          }
+          ok = ok && lo < t[0] && t[0] < t[1] && t[1] < t[2] && t[2] < hi;
+          if (!ok) {
+            const uint32_t q = (hi - lo) >> 2;
+#pragma unroll
+            for (int j = 0; j < 3; ++j) t[j] = q ? lo + q * (j + 1) - 1u : min(lo + j, hi);
+          }
           first = false;
-        } else {
-#pragma unroll
-          for (int j = 0; j < 3; ++j) t[j] = q ? lo + q * (j + 1) - 1u : min(lo + j, hi);   // lo <= t0 <= t1 <= t2 <= hi
         }
-        float ms[3] = {0.f, 0.f, 0.f};
+        float ms[3] = {0.f, 0.f, 0.f};              // weight{key > t[j]}
+        int cn[3] = {0, 0, 0};                      // #{key > t[j]}
+#pragma unroll 3
+        for (int v = tid; v < V; v += kConsumerThreads) {
+          const uint32_t k = sk[v];
+          const float wgt = ones ? 1.f : ev[v];
 #pragma unroll
-        for (int i = 0; i < kVPerThread; ++i) {
-#pragma unroll
-          for (int j = 0; j < 3; ++j) ms[j] += (key[i] > t[j]) ? e[i] : 0.f;
+          for (int j = 0; j < 3; ++j) {
+            const bool gt = k > t[j];
+            ms[j] += gt ? wgt : 0.f;
+            cn[j] += gt ? 1 : 0;
+          }
         }
-        block_sum_k<3>(ms, rbuf + par * 32);
-        par ^= 1;
-        // pred(T) = mass{key > T} < lim is false..false true..true in T; answer = smallest T with pred
-        if (ms[0] < lim) hi = t[0];
-        else if (ms[1] < lim) { lo = t[0] + 1u; hi = t[1]; }
-        else if (ms[2] < lim) { lo = t[1] + 1u; hi = t[2]; }
-        else lo = t[2] + 1u;
+        {   // block sums with one barrier: float tree as block_sum_k, integer counts through redux
+          const int lane = tid & 31, w = tid >> 5;
+          float* buf = rbuf + par * 48;
+          par ^= 1;
+#pragma unroll
+          for (int j = 0; j < 3; ++j) {
+            ms[j] = warp_sum(ms[j]);
+            cn[j] = __reduce_add_sync(0xffffffffu, cn[j]);
+          }
+          if (lane == 0) {
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+              buf[w * 6 + j] = ms[j];
+              buf[w * 6 + 3 + j] = __int_as_float(cn[j]);
+            }
+          }
+          consumer_sync();
+#pragma unroll
+          for (int j = 0; j < 3; ++j) {
+            ms[j] = ((buf[0 * 6 + j] + buf[4 * 6 + j]) + (buf[2 * 6 + j] + buf[6 * 6 + j])) +
+                    ((buf[1 * 6 + j] + buf[5 * 6 + j]) + (buf[3 * 6 + j] + buf[7 * 6 + j]));
+            int tot = 0;
+#pragma unroll
+            for (int ww = 0; ww < kNW; ++ww) tot += __float_as_int(buf[ww * 6 + 3 + j]);
+            cn[j] = tot;
+          }
+        }
+        // pred(T) = weight{key > T} < lim is false..false true..true in T; answer = smallest T with pred
+        if (ms[0] < lim) { hi = t[0]; m_hi = ms[0]; n_hi = cn[0]; }
+        else if (ms[1] < lim) { lo = t[0] + 1u; n_lo = cn[0]; hi = t[1]; m_hi = ms[1]; n_hi = cn[1]; }
+        else if (ms[2] < lim) { lo = t[1] + 1u; n_lo = cn[1]; hi = t[2]; m_hi = ms[2]; n_hi = cn[2]; }
+        else { lo = t[2] + 1u; n_lo = cn[2]; }
       }
       kmin = lo;
+      n_keep = n_lo;                                // upper bound is all the next pass needs
     }
     consumer_sync();                               // ev[] complete before the vocabulary-ordered reads
     prof_mark(P, c, 33);
@@ -199,7 +289,7 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
     float loc = 0.f;
 #pragma unroll kSmpUnroll
     for (int v = v0; v < vend; ++v) {
-      const float e = (key_of(sc[v]) >= kmin) ? ev[v] : 0.f;
+      const float e = (sk[v] >= kmin) ? ev[v] : 0.f;
       ev[v] = e;                                   // own range only: kept mass, re-read below
       loc += e;
     }

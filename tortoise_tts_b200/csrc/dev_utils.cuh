@@ -72,6 +72,12 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
       : "memory");
 }
 
+// 16-byte asynchronous copy global (L2, never L1) -> shared, and the wait for all of this thread's copies
+__device__ __forceinline__ void cp_async_cg16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 // ---- loads that must see other CTAs' writes (activations, KV written this launch): L2 only -----------------
 __device__ __forceinline__ uint4 ld_cg_u4(const void* p) { return __ldcg(reinterpret_cast<const uint4*>(p)); }
 __device__ __forceinline__ float4 ld_cg_f4(const void* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
