@@ -617,8 +617,11 @@ __device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pi
 // Acquire side: everything other CTAs write during the launch is read with ld.global.cg (L2, the coherence point)
 // and those loads are issued after the poll load has returned the final count, so no gpu-scope fence (and no L1
 // invalidate) is needed after the poll; TTS_AR_DBG bit 1 puts the fence back (A/B switch).
+// `stage` (optional): `nstage` contiguous fp32 vectors of kD floats (LayerNorm gains / biases of the next phase) that
+// warps 4..7 copy into the start of the reduction buffer while thread 0 polls, so the LayerNorm after the barrier
+// reads them from shared memory instead of paying an L2 round trip between its statistics and its output.
 __device__ __forceinline__ bool dec_grid_barrier(const Params& P, const Smem& sm, uint32_t& epoch, Feeder& fd, int extra,
-                                                 int prof_slot = -1) {
+                                                 int prof_slot = -1, const float* stage = nullptr, int nstage = 0) {
   Ctrl* c = sm.ctrl;
   // bring-up: arrival / release time of every CTA at the three barriers of one layer (scripts/stage_prof.py)
   const bool rec = P.prof && prof_slot >= 0 && threadIdx.x == 0;
@@ -634,6 +637,12 @@ __device__ __forceinline__ bool dec_grid_barrier(const Params& P, const Smem& sm
     if (threadIdx.x == 0) red_release_add_u32(P.bar_counter, 1u);
     __syncwarp();
     if (refill_n) feed(P, c, sm.ring, fd.f, refill_n, fd.head, fd.rank, fd.ht0, fd.hcnt);
+  }
+  if (threadIdx.x >= 128 && nstage) {
+    const int t = threadIdx.x - 128;                  // 0..127: 16-byte pieces t, t + 128, ...
+#pragma unroll 1
+    for (int k = t; k < nstage * (kD / 4); k += 128) cp_async_cg16(sm.red + 4 * k, stage + 4 * k);
+    cp_async_wait_all();
   }
   if (threadIdx.x == 0) {
     const uint32_t target = epoch * (uint32_t)P.G;
@@ -705,7 +714,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       // ---- phase A: ln_1 -> q,k,v of this head -> attention -> split-K c_proj -> y ----
       prof_mark(P, c, 100 + OP_LN_QKV);
       const int pslot = (step == P.prof_step && layer == 3) ? 0 : -4;
-      alive = dec_grid_barrier(P, sm, epoch, fd, 0, pslot);
+      alive = dec_grid_barrier(P, sm, epoch, fd, 0, pslot, layer_f(P, layer) + kFOffLn1g, 2);
       if (!alive) break;
       prof_mark(P, c, 200 + OP_LN_QKV);
       if (layer == 0 && ld_cg_i(P.n_active) == 0) { alive = false; break; }
@@ -713,7 +722,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       ins.op = OP_LN_QKV; ins.flags = 0;
       ProjAdd padd;
       proj_preload(P, layer, head, rank, row_lo, padd);
-      ln_cluster<false>(P, ins, sm, P.x, layer_f(P, layer) + kFOffLn1g, layer_f(P, layer) + kFOffLn1b, nullptr, nullptr, rank, head, layer + 1);
+      ln_cluster<false>(P, ins, sm, P.x, sm.red, sm.red + kD, nullptr, nullptr, rank, head, layer + 1);
       cluster_barrier();
       prof_mark(P, c, 1);
       {
@@ -742,11 +751,11 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       proj_splitk(P, layer, head, rank, row_lo, sm, pipe, padd);
       // ---- phase B: ln_2 -> c_fc -> gelu_new ----
       prof_mark(P, c, 100 + OP_LN_FC);
-      alive = dec_grid_barrier(P, sm, epoch, fd, 2, pslot + 1);     // + the two split-K c_proj slots
+      alive = dec_grid_barrier(P, sm, epoch, fd, 2, pslot + 1, layer_f(P, layer) + kFOffLn2g, 2);   // + the two split-K c_proj slots
       if (!alive) break;
       prof_mark(P, c, 200 + OP_LN_FC);
       ins.op = OP_LN_FC; ins.flags = F_FIXED_SRC;
-      ln_cluster<false>(P, ins, sm, P.x, layer_f(P, layer) + kFOffLn2g, layer_f(P, layer) + kFOffLn2b, nullptr, nullptr, rank, head, -1);
+      ln_cluster<false>(P, ins, sm, P.x, sm.red, sm.red + kD, nullptr, nullptr, rank, head, -1);
       cluster_barrier();
       prof_mark(P, c, 1);
       {
@@ -768,11 +777,11 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
     }
     if (!alive) break;
     prof_mark(P, c, 100 + OP_HEAD);
-    alive = dec_grid_barrier(P, sm, epoch, fd, 0);
+    alive = dec_grid_barrier(P, sm, epoch, fd, 0, -1, P.lnf_g, 4);      // lnf_g, lnf_b, fn_g, fn_b are contiguous (tts_ar.cu)
     if (!alive) break;
     prof_mark(P, c, 200 + OP_HEAD);
     ins.op = OP_HEAD; ins.layer = 0; ins.flags = 0;
-    ln_cluster<true>(P, ins, sm, P.x, P.lnf_g, P.lnf_b, P.fn_g, P.fn_b, rank, head, 0);
+    ln_cluster<true>(P, ins, sm, P.x, sm.red, sm.red + kD, sm.red + 2 * kD, sm.red + 3 * kD, rank, head, 0);
     cluster_barrier();
     for (int tb = 0; tb < hcnt; tb += 6) {
       const int t0 = ht0 + tb;

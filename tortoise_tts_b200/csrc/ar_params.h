@@ -146,6 +146,7 @@ constexpr long long kOffProj2 = kOffFc + (long long)(kD4 / 8) * kU4PerChunkP;
 constexpr long long kOffProjk = kOffProj2 + (long long)(kD / 8) * 4 * kU4PerChunkP;
 constexpr int kFOffLn1g = 0, kFOffLn1b = kD, kFOffLn2g = 2 * kD, kFOffLn2b = 3 * kD, kFOffBqkv = 4 * kD,
               kFOffBproj = 4 * kD + kD3, kFOffBfc = 5 * kD + kD3, kFOffBproj2 = 5 * kD + kD3 + kD4;
+static_assert(kFOffLn1b == kFOffLn1g + kD && kFOffLn2b == kFOffLn2g + kD, "ar_decode.cu stages (gain, bias) pairs as one block");
 
 // dynamic shared memory layout of the interpreter kernel
 constexpr int kSmemCtrlBytes = 1024;
