@@ -99,9 +99,18 @@ __device__ __forceinline__ int* rinfo_ptr(const Smem& sm) { return reinterpret_c
 constexpr int kCtxOffsetFloats = 7680;
 __device__ __forceinline__ uint4* ctx_smem(const Smem& sm) { return reinterpret_cast<uint4*>(sm.red + kCtxOffsetFloats); }
 
+// Called by warps 4..7 only (threads 128..255), which are idle while warps 0..3 normalise: the dependent loads overlap
+// the LayerNorm instead of preceding it.  Ends with a named barrier over those 128 threads; everyone else sees the
+// facts after the cluster barrier that follows the LayerNorm.
 __device__ void build_rinfo(const Params& P, int rbase, const Smem& sm) {
   int* ri = rinfo_ptr(sm);
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x - 128;
+  {
+    const int j = tid >> 6, i = tid & 63, row = rbase + j;
+    int v = 0;
+    if (row < P.n_rows) v = (i < 32) ? P.prefix_pt[P.row_utt[row] * kMaxPagesPerSeg + i] : P.priv_pt[row * kMaxPagesPerSeg + (i - 32)];
+    ri[64 + 64 * j + i] = v;
+  }
   if (tid < 16) {
     const int row = tid;
     const int pos = (row < P.n_rows) ? ld_cg_i(P.row_pos + row) : -1;
@@ -118,13 +127,8 @@ __device__ void build_rinfo(const Params& P, int rbase, const Smem& sm) {
     const int pos = (row < P.n_rows) ? ld_cg_i(P.row_pos + row) : -1;
     ri[32 + j] = pos + 1;
     ri[34 + j] = (row < P.n_rows) ? P.utt_plen[P.row_utt[row]] : 0;
-  } else if (tid >= 64 && tid < 192) {
-    const int j = (tid - 64) >> 6, i = (tid - 64) & 63, row = rbase + j;
-    int v = 0;
-    if (row < P.n_rows) v = (i < 32) ? P.prefix_pt[P.row_utt[row] * kMaxPagesPerSeg + i] : P.priv_pt[row * kMaxPagesPerSeg + (i - 32)];
-    ri[64 + 64 * j + i] = v;
   }
-  consumer_sync();
+  asm volatile("bar.sync 2, 128;" ::: "memory");
 }
 
 // ---- cluster-cooperative LayerNorm: CTA rank r normalises rows 4r..4r+3 (warps 0..3, one row each) and writes
@@ -132,9 +136,10 @@ __device__ void build_rinfo(const Params& P, int rbase, const Smem& sm) {
 // 16 rows are read from L2 once per cluster instead of once per CTA.  Warps 4..7 meanwhile pull the NEXT layer's
 // K/V pages of this CTA's attention rows into L2 (bulk prefetch), so the attention phase is not an HBM stall.
 // The caller follows with cluster_barrier().
-template <bool kDouble>
-__device__ void ln_cluster(const Params& P, const Instr& ins, const Smem& sm, const float* src, const float* g1, const float* b1,
-                           const float* g2, const float* b2, int rank, int head, int pf_layer) {
+// `gb` = the staged (gain, bias) vectors: one pair, or two for the head (ln_f then final_norm, `dbl`); the head is the
+// same call site as ln_1 on purpose -- code that runs once per step is fetched cold, code shared with the layers is not.
+__device__ __forceinline__ void ln_cluster(const Params& P, const Instr& ins, const Smem& sm, const float* src, const float* gb, bool dbl,
+                                           int rank, int head, int pf_layer, int rinfo_rbase) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   if (w < 4) {
     const int r = 4 * rank + w;
@@ -143,15 +148,14 @@ __device__ void ln_cluster(const Params& P, const Instr& ins, const Smem& sm, co
     float4 v[8];
     ln_load_row(P, ins, src, lrow, lane, v);
     prof_mark(P, sm.ctrl, 21);
-    ln_normalise(v, g1, b1, lane);
+    const int npass = dbl ? 2 : 1;
+#pragma unroll 1
+    for (int p = 0; p < npass; ++p) ln_normalise(v, gb + 2 * p * kD, gb + (2 * p + 1) * kD, lane);
     prof_mark(P, sm.ctrl, 22);
-    if (kDouble) {
-      ln_normalise(v, g2, b2, lane);
-      if (ins.op == OP_HEAD && blockIdx.x < kClusterSize && ok) {
-        float* lp = P.cur_latent + (size_t)lrow * kD;
+    if (dbl && blockIdx.x < kClusterSize && ok) {      // final_norm(ln_f(x)): the latent of this step
+      float* lp = P.cur_latent + (size_t)lrow * kD;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) *reinterpret_cast<float4*>(lp + 128 * j + 4 * lane) = v[j];
-      }
+      for (int j = 0; j < 8; ++j) *reinterpret_cast<float4*>(lp + 128 * j + 4 * lane) = v[j];
     }
     uint8_t* dst = sm.a_rm + (size_t)r * kARowBytes;
 #pragma unroll
@@ -162,6 +166,7 @@ __device__ void ln_cluster(const Params& P, const Instr& ins, const Smem& sm, co
     }
     prof_mark(P, sm.ctrl, 23);
   } else {
+    if (rinfo_rbase >= 0) build_rinfo(P, rinfo_rbase, sm);
     if (pf_layer >= 0 && pf_layer <= P.n_layers) {
     const int t = threadIdx.x - 128;                 // 0..127
     // the small fp32 parameters (LN gains/biases, GEMM biases: one contiguous block per layer, tts_ar.cu) are
@@ -709,22 +714,25 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
     ins.nrows = n;
     steps_done = step + 1;
     if (P.skip_last_model && step == P.n_steps - 1) break;
-    for (int layer = 0; layer < P.n_layers && alive; ++layer) {
-      ins.layer = layer;
+    // layer == n_layers is the head: ln_f + final_norm through the same LayerNorm code as ln_1, then the vocabulary GEMM
+    for (int layer = 0; layer <= P.n_layers && alive; ++layer) {
+      const bool is_head = layer == P.n_layers;
+      ins.layer = is_head ? 0 : layer;
       // ---- phase A: ln_1 -> q,k,v of this head -> attention -> split-K c_proj -> y ----
-      prof_mark(P, c, 100 + OP_LN_QKV);
+      prof_mark(P, c, 100 + (is_head ? OP_HEAD : OP_LN_QKV));
       const int pslot = (step == P.prof_step && layer == 3) ? 0 : -4;
-      alive = dec_grid_barrier(P, sm, epoch, fd, 0, pslot, layer_f(P, layer) + kFOffLn1g, 2);
+      // gains / biases to stage: ln_1 (g, b), or lnf_g, lnf_b, fn_g, fn_b (contiguous, tts_ar.cu) for the head
+      alive = dec_grid_barrier(P, sm, epoch, fd, 0, pslot, is_head ? P.lnf_g : layer_f(P, layer) + kFOffLn1g, is_head ? 4 : 2);
       if (!alive) break;
-      prof_mark(P, c, 200 + OP_LN_QKV);
+      prof_mark(P, c, 200 + (is_head ? OP_HEAD : OP_LN_QKV));
       if (layer == 0 && ld_cg_i(P.n_active) == 0) { alive = false; break; }
-      if (layer == 0) build_rinfo(P, row_lo + 2 * rank, sm);
-      ins.op = OP_LN_QKV; ins.flags = 0;
+      ins.op = is_head ? OP_HEAD : OP_LN_QKV; ins.flags = 0;
       ProjAdd padd;
-      proj_preload(P, layer, head, rank, row_lo, padd);
-      ln_cluster<false>(P, ins, sm, P.x, sm.red, sm.red + kD, nullptr, nullptr, rank, head, layer + 1);
+      if (!is_head) proj_preload(P, layer, head, rank, row_lo, padd);
+      ln_cluster(P, ins, sm, P.x, sm.red, is_head, rank, head, is_head ? 0 : layer + 1, layer == 0 ? row_lo + 2 * rank : -1);
       cluster_barrier();
       prof_mark(P, c, 1);
+      if (is_head) break;
       {
         const float* bias = layer_f(P, layer) + kFOffBqkv;
         const int* ri = rinfo_ptr(sm);
@@ -755,7 +763,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       if (!alive) break;
       prof_mark(P, c, 200 + OP_LN_FC);
       ins.op = OP_LN_FC; ins.flags = F_FIXED_SRC;
-      ln_cluster<false>(P, ins, sm, P.x, sm.red, sm.red + kD, nullptr, nullptr, rank, head, -1);
+      ln_cluster(P, ins, sm, P.x, sm.red, false, rank, head, -1, -1);
       cluster_barrier();
       prof_mark(P, c, 1);
       {
@@ -776,13 +784,6 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       if (c->abort_flag) alive = false;
     }
     if (!alive) break;
-    prof_mark(P, c, 100 + OP_HEAD);
-    alive = dec_grid_barrier(P, sm, epoch, fd, 0, -1, P.lnf_g, 4);      // lnf_g, lnf_b, fn_g, fn_b are contiguous (tts_ar.cu)
-    if (!alive) break;
-    prof_mark(P, c, 200 + OP_HEAD);
-    ins.op = OP_HEAD; ins.layer = 0; ins.flags = 0;
-    ln_cluster<true>(P, ins, sm, P.x, sm.red, sm.red + kD, sm.red + 2 * kD, sm.red + 3 * kD, rank, head, 0);
-    cluster_barrier();
     for (int tb = 0; tb < hcnt; tb += 6) {
       const int t0 = ht0 + tb;
       gemm16<6, false, true>(P, sm, pipe, fd, min(6, hcnt - tb), 0, P.b_head, [&](int i) { return t0 + i; },
