@@ -286,7 +286,13 @@ def test_ragged_batch_equals_single_utterance_runs(b200):
 
 
 @pytest.mark.parametrize("kw", [dict(top_p=0.8, temperature=0.8, top_k=0), dict(top_k=16, temperature=1.3, top_p=1.0),
-                                dict(top_k=50, top_p=0.5, temperature=0.7, repetition_penalty=2.0)])
+                                dict(top_k=50, top_p=0.5, temperature=0.7, repetition_penalty=2.0),
+                                # edges of the count-terminated threshold search: a one-token support, a nucleus of a
+                                # few tokens on a peaked row (first probe round ends it), an almost complete nucleus on
+                                # a flat row (most rounds), k close to the vocabulary size
+                                dict(top_k=1, temperature=1.0, top_p=1.0), dict(top_k=0, top_p=0.02, temperature=1.0),
+                                dict(top_k=50, top_p=0.8, temperature=0.02), dict(top_k=0, top_p=0.999, temperature=3.0),
+                                dict(top_k=8000, top_p=0.9, temperature=1.0, repetition_penalty=1.5)])
 def test_device_sampler_equals_oracle_on_device_logits(b200, kw):
     """The fused warpers + Philox inverse-CDF multinomial vs the oracle's HF-equivalent processors
     (pinned to HF's own classes by tests/test_oracle_golden.py) applied to the DEVICE's logits: identical

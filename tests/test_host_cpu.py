@@ -172,3 +172,95 @@ def test_gather_codes_world2_gloo(tmp_path):
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
         assert "ok" in o
+
+
+# ---- the device sampler's threshold search, restated in numpy (csrc/ar_sample.cuh) ---------------------------------
+def _keys(a):
+    b = a.astype(np.float32).view(np.uint32).astype(np.uint64)
+    return np.where(b & 0x80000000, (~b) & 0xFFFFFFFF, b | 0x80000000).astype(np.uint64)
+
+
+def _key_to_float(k):
+    b = (k & 0x7FFFFFFF) if (k & 0x80000000) else ((~k) & 0xFFFFFFFF)
+    return np.uint32(b).view(np.float32)
+
+
+def _threshold_search(keys, wgt, lim, lo, n_lo, smin, smax):
+    """Smallest key T in [lo, kmax] with weight{key > T} < lim: 4-way rounds over the score interval that also count
+    the tokens left inside; <= 32 of them end the search with a descending sort + prefix sum.  Returns (T, rounds)."""
+    f32 = np.float32
+    kmax = int(keys.max())
+    hi, n_hi, m_hi, first, rounds = kmax, 0, f32(0), True, 0
+    while lo < hi:
+        if n_lo - n_hi <= 32:
+            sel = (keys >= lo) & (keys <= hi)
+            order = np.argsort(-keys[sel].astype(np.int64), kind="stable")
+            ck, cw = keys[sel][order], wgt[sel][order]
+            incl = np.cumsum(cw, dtype=np.float32)
+            brk = np.nonzero(m_hi + incl >= lim)[0]
+            if len(brk):
+                lo = int(ck[brk[0]])
+            break
+        fl, fh = max(_key_to_float(lo), f32(smin)), _key_to_float(hi)
+        t, ok = [], True
+        for j in range(3):
+            with np.errstate(all="ignore"):
+                pj = f32(fl + (fh - fl) * f32(0.25 * (j + 1)))
+                if first:
+                    pj = max(pj, f32(smax - (16.0, 4.0, 1.0)[j])) if np.isfinite(pj) else f32(smax - (16.0, 4.0, 1.0)[j])
+            ok = ok and bool(np.abs(pj) <= 3.0e38)
+            t.append(int(_keys(np.array([pj], np.float32))[0]))
+        ok = ok and lo < t[0] < t[1] < t[2] < hi
+        if not ok:
+            q = (hi - lo) >> 2
+            t = [lo + q * (j + 1) - 1 if q else min(lo + j, hi) for j in range(3)]
+        first = False
+        rounds += 1
+        ms = [wgt[keys > tj].sum(dtype=np.float32) for tj in t]
+        cn = [int((keys > tj).sum()) for tj in t]
+        if ms[0] < lim:
+            hi, m_hi, n_hi = t[0], ms[0], cn[0]
+        elif ms[1] < lim:
+            lo, n_lo, hi, m_hi, n_hi = t[0] + 1, cn[0], t[1], ms[1], cn[1]
+        elif ms[2] < lim:
+            lo, n_lo, hi, m_hi, n_hi = t[1] + 1, cn[1], t[2], ms[2], cn[2]
+        else:
+            lo, n_lo = t[2] + 1, cn[2]
+    return lo, rounds
+
+
+@pytest.mark.parametrize("std,top_k,top_p", [(0.02, 0, 0.8), (1.0, 50, 0.8), (6.0, 0, 0.5), (0.5, 16, 1.0),
+                                             (3.0, 8000, 0.9), (1.0, 1, 1.0), (0.1, 0, 0.02)])
+def test_threshold_search_keeps_the_hf_support_set(std, top_k, top_p):
+    """The search the device sampler runs for top-k and top-p (one routine, ar_sample.cuh) selects exactly HF's
+    TopKLogitsWarper / TopPLogitsWarper support (oracle.uv_oracle, pinned to HF's classes by test_oracle_golden.py),
+    ties included, in a handful of rounds instead of 16 key-space bisection steps."""
+    from oracle.uv_oracle import apply_top_k, apply_top_p
+    rng = np.random.default_rng(int(std * 100) + top_k)
+    V = 8194
+    for trial in range(3):
+        sc = rng.normal(0, std, V).astype(np.float32)
+        sc[rng.integers(0, V, 40)] = sc[rng.integers(0, V, 40)]            # ties
+        keys = _keys(sc)
+        smin, smax = sc.min(), sc.max()
+        kmin, n_keep, rounds = int(_keys(np.array([-np.inf], np.float32))[0]), V, 0
+        if 0 < top_k < V:
+            kmin, r = _threshold_search(keys, np.ones(V, np.float32), np.float32(top_k), kmin, n_keep, smin, smax)
+            n_keep, rounds = int((keys >= kmin).sum()), rounds + r
+        e = np.where(keys >= kmin, np.exp(sc - smax), 0).astype(np.float32)
+        if top_p < 1.0:
+            lim = np.float32(top_p) * e.sum(dtype=np.float32)
+            kmin, r = _threshold_search(keys, e, lim, kmin, n_keep, smin, smax)
+            rounds += r
+        ref = apply_top_p(apply_top_k(torch.from_numpy(sc)[None], top_k), top_p)[0]
+        ref_keep = torch.isfinite(ref).numpy()
+        mine = keys >= kmin
+        # the nucleus edge may differ by the tokens whose cumulative mass is within fp32 summation error of p
+        diff = np.nonzero(mine != ref_keep)[0]
+        if len(diff):
+            p = torch.softmax(apply_top_k(torch.from_numpy(sc)[None], top_k)[0].double(), -1).numpy()
+            order = np.argsort(-sc, kind="stable")
+            cum_excl = np.empty(V)
+            cum_excl[order] = np.cumsum(p[order]) - p[order]
+            assert np.all(np.abs(cum_excl[diff] - top_p) < 1e-4), (diff[:5], cum_excl[diff][:5])
+        assert rounds <= 16, rounds
