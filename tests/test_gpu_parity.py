@@ -291,12 +291,15 @@ def test_ragged_batch_equals_single_utterance_runs(b200):
                                 # few tokens on a peaked row (first probe round ends it), an almost complete nucleus on
                                 # a flat row (most rounds), k close to the vocabulary size
                                 dict(top_k=1, temperature=1.0, top_p=1.0), dict(top_k=0, top_p=0.02, temperature=1.0),
-                                dict(top_k=50, top_p=0.8, temperature=0.02), dict(top_k=0, top_p=0.999, temperature=3.0),
-                                dict(top_k=8000, top_p=0.9, temperature=1.0, repetition_penalty=1.5)])
+                                dict(top_k=50, top_p=0.8, temperature=0.02), dict(top_k=0, top_p=0.999, temperature=3.0, min_checked=0.5),
+                                dict(top_k=8000, top_p=0.9, temperature=1.0, repetition_penalty=1.5, min_checked=0.5)])
 def test_device_sampler_equals_oracle_on_device_logits(b200, kw):
     """The fused warpers + Philox inverse-CDF multinomial vs the oracle's HF-equivalent processors
     (pinned to HF's own classes by tests/test_oracle_golden.py) applied to the DEVICE's logits: identical
     tokens except where u*Z is within fp32 summation-order distance of a CDF edge."""
+    kw = dict(kw)
+    # a flat row that keeps ~8000 tokens has CDF steps of 1.2e-4: a third of the draws fall within the 1e-5 skip margin
+    min_checked = kw.pop("min_checked", 0.9)
     m, o, cfg, lat, texts = make_small(b200, U=1, T=12, max_utts=1, max_seqs=24, max_new_tokens=16)
     text = torch.stack(texts)
     N, seed, base = 24, 4321, 1000
@@ -323,7 +326,7 @@ def test_device_sampler_equals_oracle_on_device_logits(b200, kw):
                 assert int(out[r]) == tok, (step, r, int(out[r]), tok, margin)
                 n_checked += 1
         ids = torch.cat([ids, out[:, None]], 1)
-    assert n_checked > 0.9 * 6 * N
+    assert n_checked > min_checked * 6 * N
     m.close()
 
 
