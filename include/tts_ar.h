@@ -169,6 +169,16 @@ int tts_ar_inference_speech_host(TtsArHandle* h, const float* latent_host, const
                                  int32_t n_cand, const TtsArSampling* s, int32_t max_new,
                                  int64_t* out_codes_host, int32_t* steps_run);
 
+/* Epilogue between the sampler and its callers, in place on device codes [rows][stride] (int64):
+ * reference tortoise_tts/inference.py:353-366 (and train.py:135-147): in a row that contains the stop token, it and
+ * everything after it become `calm_token` (83) and the row's last three codes become 45, 45, 248; a row without a
+ * stop token is left alone and reported as first_stop = -1 (the reference raises on it: `.min()` of an empty index
+ * tensor, inference.py:355 -- the caller decides).  trim_len[r] = first index at which more than 8 consecutive calm
+ * tokens have been seen in the fixed row, `len` if never (inference.py:381-389 cuts the latents of every row at
+ * trim_len[0]).  first_stop / trim_len: device int32[rows], nullable.  ASYNC on `stream`. */
+int tts_ar_fixup_codes(TtsArHandle* h, int64_t* codes, int32_t rows, int32_t len, int32_t stride, int32_t calm_token,
+                       int32_t* first_stop, int32_t* trim_len, void* stream);
+
 /* Parity hook: copies `bytes` of an internal device buffer to dst (dev).  name: "x" (residual stream, fp32
  * [rows,1024]), "q", "logits", "cur_latent", "kv" (page pool, bf16), "ctx", "h" (bf16 fragment order). */
 int tts_ar_debug_copy(TtsArHandle* h, const char* name, void* dst, uint64_t bytes, void* stream);

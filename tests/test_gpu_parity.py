@@ -422,3 +422,43 @@ def test_c2_shape_properties(full_model):
     assert len({tuple(r.tolist()) for r in a}) == 16
     b = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=16, max_generate_length=120, **kw).cpu()
     assert torch.equal(a[:, :120], b)
+
+
+def test_fixup_codes_epilogue_bit_exact(b200, golden_dir):
+    """the stop-token fix-up + calm-token trim as a device epilogue (tts_ar_fixup_codes) against the
+    vectors produced by exec'ing the reference's own loops (tests/golden/fixup.npz), against the oracle on random rows
+    at BASELINE sizes (16 x 500, 256 x 604), on a strided view, and through its size-independent properties."""
+    from oracle.fixup import fixup_codes, calm_trim
+    m, o, cfg, lat, texts = make_small(b200, U=1, T=8, max_utts=1, max_seqs=2, max_new_tokens=8)
+    g = np.load(os.path.join(golden_dir, "fixup.npz"))
+    for i in range(int(g["n_cases"])):
+        codes = torch.from_numpy(g[f"in_{i}"]).cuda()
+        out, trim = m.fix_autoregressive_codes(codes)
+        assert out.data_ptr() == codes.data_ptr()                        # in place, like the reference
+        assert torch.equal(out.cpu(), torch.from_numpy(g[f"out_{i}"])), i
+        assert trim == int(g["trims"][i]), i
+    rng = np.random.default_rng(5)
+    for rows, n in [(16, 500), (256, 604), (1, 3), (7, 33)]:
+        codes = rng.integers(0, 8192, size=(rows, n)).astype(np.int64)
+        codes[rng.random(size=codes.shape) < 0.05] = 83
+        for r in range(rows):
+            codes[r, int(rng.integers(0, n)):] = 8193
+        ref, first = fixup_codes(codes)
+        wide = torch.full((rows, n + 13), -7, dtype=torch.int64, device="cuda")   # strided view: stride > len
+        view = wide[:, :n]
+        view.copy_(torch.from_numpy(codes))
+        out, trim = m.fix_autoregressive_codes(view)
+        assert torch.equal(out.cpu(), torch.from_numpy(ref))
+        assert trim == calm_trim(ref)
+        assert bool((wide[:, n:] == -7).all())                           # nothing written past the row
+        # properties: no stop token survives, so a second pass finds nothing to fix (strict would raise)
+        assert not bool((out == 8193).any())
+        again, trim2 = m.fix_autoregressive_codes(out.clone(), strict=False)
+        assert torch.equal(again, out) and trim2 == trim
+        with pytest.raises(RuntimeError):
+            m.fix_autoregressive_codes(out.clone())
+    with pytest.raises(ValueError):
+        m.fix_autoregressive_codes(torch.zeros(2, 8, dtype=torch.int32, device="cuda"))
+    with pytest.raises(ValueError):                                      # len < 3: BAD_ARG from the C ABI
+        m.fix_autoregressive_codes(torch.full((1, 2), 8193, dtype=torch.int64, device="cuda"))
+    m.close()

@@ -4,6 +4,7 @@ import ast
 import os
 
 import numpy as np
+import pytest
 import torch
 
 from oracle import philox
@@ -108,3 +109,21 @@ def test_multinomial_row_is_inverse_cdf():
     pr = e / e.sum()
     chi2 = (((counts - 4000 * pr) ** 2) / np.maximum(4000 * pr, 1e-9))[pr > 0].sum()
     assert chi2 < 2.0 * (pr > 0).sum() + 30
+
+
+def test_fixup_oracle_matches_the_executed_reference_lines(golden_dir):
+    """oracle/fixup.py vs tests/golden/fixup.npz, which oracle/make_golden_fixup.py produced by exec'ing the reference's
+    own stop-token fix-up and calm-token trim loops (inference.py:353-366, 381-389).  Bit-exact (integer work)."""
+    from oracle.fixup import fixup_codes, calm_trim
+    g = np.load(os.path.join(golden_dir, "fixup.npz"))
+    for i in range(int(g["n_cases"])):
+        fixed, first = fixup_codes(g[f"in_{i}"])
+        assert np.array_equal(fixed, g[f"out_{i}"]), i
+        assert calm_trim(fixed) == int(g["trims"][i]), i
+        assert np.array_equal(first, np.argmax(g[f"in_{i}"] == 8193, axis=1)), i
+    # a row without a stop token: the reference raises (Q10); non-strict leaves it alone
+    row = np.arange(20, dtype=np.int64)[None]
+    with pytest.raises(RuntimeError):
+        fixup_codes(row)
+    fixed, first = fixup_codes(row, strict=False)
+    assert np.array_equal(fixed, row) and first[0] == -1 and calm_trim(fixed) == 20

@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libtts_ar.so")
 SYMBOLS = [
     "tts_ar_abi_version", "tts_ar_create", "tts_ar_destroy", "tts_ar_last_error", "tts_ar_load_weights",
     "tts_ar_prefill", "tts_ar_generate", "tts_ar_step", "tts_ar_logits_debug", "tts_ar_forward_latents",
-    "tts_ar_inference_speech_host", "tts_ar_sync_result", "tts_ar_debug_copy",
+    "tts_ar_inference_speech_host", "tts_ar_sync_result", "tts_ar_debug_copy", "tts_ar_fixup_codes",
 ]
 
 STATUS = {0: "OK", -1: "BAD_ARG", -2: "CAPACITY", -3: "CUDA", -4: "STATE", -5: "DEVICE", -6: "WATCHDOG"}
@@ -82,6 +82,7 @@ def load():
                                                  C.POINTER(TtsArSampling), i32, i64p, C.POINTER(C.c_int32)]
     lib.tts_ar_sync_result.argtypes = [vp, C.POINTER(TtsArStats), vp]
     lib.tts_ar_debug_copy.argtypes = [vp, C.c_char_p, vp, C.c_uint64, vp]
+    lib.tts_ar_fixup_codes.argtypes = [vp, i64p, i32, i32, i32, i32, i32p, i32p, vp]
     for s in SYMBOLS:
         getattr(lib, s)
         if s not in ("tts_ar_destroy", "tts_ar_last_error"):

@@ -217,6 +217,51 @@ void launch_reset_sampler(int n_seqs, int seen_words, uint32_t* seen, int* finis
                                                         start_mel, attn_cnt, n_cnt);
 }
 
+// ---- stop-token fix-up + calm-token trim of the generated codes (reference inference.py:353-366, 381-389; the same
+// loop in train.py:135-147, 161-169): one CTA per row.
+//   row has a stop token at first index s:  codes[s:] = calm (83); then the last three codes = 45, 45, 248
+//   row has none: untouched, first_stop = -1 (the reference raises on such a row, quirk Q10: the adapter decides)
+//   trim[r] = first index k at which more than 8 consecutive calm tokens have been seen (row length if never):
+//   the reference cuts the latents of ALL rows at trim[0].
+__global__ void fixup_codes_kernel(long long* __restrict__ codes, int len, int stride, int stop, int calm, int* first_stop,
+                                   int* trim) {
+  __shared__ int s_first, s_trim;
+  long long* row = codes + (size_t)blockIdx.x * stride;
+  if (threadIdx.x == 0) { s_first = len; s_trim = len; }
+  __syncthreads();
+  int mine = len;
+  for (int k = threadIdx.x; k < len; k += blockDim.x)
+    if (row[k] == (long long)stop) { mine = k; break; }          // ascending per thread: the first hit is its minimum
+  if (mine < len) atomicMin(&s_first, mine);
+  __syncthreads();
+  const int s = s_first;
+  if (s < len) {
+    for (int k = s + threadIdx.x; k < len; k += blockDim.x) row[k] = calm;
+    __syncthreads();
+    if (threadIdx.x < 3 && len >= 3) row[len - 3 + threadIdx.x] = threadIdx.x == 2 ? 248 : 45;
+    __syncthreads();
+  }
+  // more than 8 consecutive calm tokens ending at k  <=>  row[k-8 .. k] are all calm
+  int t = len;
+  for (int k = 8 + threadIdx.x; k < len; k += blockDim.x) {
+    bool all = true;
+#pragma unroll
+    for (int j = 0; j < 9; ++j) all = all && row[k - j] == (long long)calm;
+    if (all) { t = k; break; }
+  }
+  if (t < len) atomicMin(&s_trim, t);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (first_stop) first_stop[blockIdx.x] = s < len ? s : -1;
+    if (trim) trim[blockIdx.x] = s_trim;
+  }
+}
+
+void launch_fixup_codes(long long* codes, int rows, int len, int stride, int stop, int calm, int* first_stop, int* trim,
+                        cudaStream_t st) {
+  fixup_codes_kernel<<<rows, 128, 0, st>>>(codes, len, stride, stop, calm, first_stop, trim);
+}
+
 cudaError_t launch_program(const Params& P, int smem_bytes, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {

@@ -23,6 +23,8 @@ struct EmbedArgs {
 void launch_pack_weight(const void* src, int dtype, uint4* dst, int K, int N, int n_tiles, int transposed, cudaStream_t st);
 void launch_to_f32(const void* src, int dtype, float* dst, size_t n, size_t n_pad, cudaStream_t st);
 void launch_embed_rows(const EmbedArgs& a, int n_rows, cudaStream_t st);
+void launch_fixup_codes(long long* codes, int rows, int len, int stride, int stop, int calm, int* first_stop, int* trim,
+                        cudaStream_t st);
 void launch_reset_sampler(int n_seqs, int seen_words, uint32_t* seen, int* finished, int* gen_count, int* row_pos,
                           int* n_active, int start_mel, int* attn_cnt, int n_cnt, cudaStream_t st);
 cudaError_t launch_program(const Params& P, int smem_bytes, cudaStream_t st);

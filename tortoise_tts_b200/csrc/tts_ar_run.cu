@@ -380,6 +380,18 @@ extern "C" int tts_ar_inference_speech_host(TtsArHandle* h, const float* latent_
   return 0;
 }
 
+extern "C" int tts_ar_fixup_codes(TtsArHandle* h, int64_t* codes, int32_t rows, int32_t len, int32_t stride, int32_t calm_token,
+                                  int32_t* first_stop, int32_t* trim_len, void* stream) {
+  if (!h || !codes) return TTS_AR_ERR_BAD_ARG;
+  if (rows < 0 || len < 3 || stride < len) return fail(h, TTS_AR_ERR_BAD_ARG, "fixup_codes: need rows >= 0, len >= 3, stride >= len");
+  if (rows == 0) return 0;
+  launch_fixup_codes(reinterpret_cast<long long*>(codes), rows, len, stride, h->cfg.stop_mel_token, calm_token, first_stop,
+                     trim_len, (cudaStream_t)stream);
+  TTS_CUDA(h, cudaGetLastError());
+  h->launches += 1;
+  return 0;
+}
+
 extern "C" int tts_ar_debug_copy(TtsArHandle* h, const char* name, void* dst, uint64_t bytes, void* stream) {
   if (!h || !name || !dst) return TTS_AR_ERR_BAD_ARG;
   const void* src = nullptr;

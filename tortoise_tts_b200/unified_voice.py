@@ -187,6 +187,28 @@ class UnifiedVoiceB200:
         self._check(self.lib.tts_ar_sync_result(self.handle, C.byref(st), self._stream()), "tts_ar_sync_result")
         return st
 
+    def fix_autoregressive_codes(self, codes, calm_token=83, strict=True):
+        """The epilogue TTS.inference / train.run_eval run on the sampled codes, on the device and in place
+        (reference inference.py:353-366, 381-389; train.py:135-147, 161-169): in every row the stop token and everything
+        after it become `calm_token`, the last three codes become 45, 45, 248.  Returns (codes, trim) where trim is the
+        index at which the reference cuts the latents (first index of row 0 with more than 8 consecutive calm tokens
+        behind it; the row length if there is none).  A row without a stop token makes the reference raise (`.min()`
+        of an empty tensor, inference.py:355): with strict=True so does this, with strict=False the row is left as is."""
+        if codes.dim() != 2 or codes.dtype != torch.int64 or not codes.is_cuda:
+            raise ValueError("codes must be a CUDA int64 tensor [rows, len]")
+        if codes.stride(1) != 1:
+            raise ValueError("codes rows must be contiguous")
+        rows, n = codes.shape
+        first = torch.empty(rows, device=codes.device, dtype=torch.int32)
+        trim = torch.empty(rows, device=codes.device, dtype=torch.int32)
+        self._check(self.lib.tts_ar_fixup_codes(self.handle, _ptr(codes), rows, n, codes.stride(0), int(calm_token), _ptr(first),
+                                                _ptr(trim), self._stream()), "tts_ar_fixup_codes")
+        first, trim = first.cpu(), trim.cpu()          # one device -> host read for both results (the reference: one per row)
+        if strict and rows and bool((first < 0).any()):
+            raise RuntimeError("min(): Expected reduction dim to be specified for input.numel() == 0. "
+                               "(a row without a stop token: reference inference.py:355)")
+        return codes, (int(trim[0]) if rows else n)
+
     def logits_debug(self):
         rows = C.c_int32(0)
         out = torch.empty(self.cfg.max_seqs, self.geometry.number_mel_codes, device=self.device, dtype=torch.float32)
