@@ -101,7 +101,9 @@ typedef struct {
   uint64_t seed;                /* Philox key */
   int64_t seq_index_base;       /* global index of local sequence 0 (multi-GPU invariance) */
   int32_t ignore_eos;           /* benchmarking: never finish, run exactly max_new steps */
-  int32_t reserved;
+  float typical_mass;           /* TypicalLogitsWarper(mass) of unified_voice.py:47-75, run as a logits PROCESSOR (:659): after
+                                   the repetition penalty, before temperature / top-k / top-p, also in greedy mode;
+                                   outside (0,1) = off (0 in zero-initialised structs) */
 } TtsArSampling;
 
 typedef struct {

@@ -125,7 +125,7 @@ class OracleAR:
     # ---- sample loop ----------------------------------------------------------------------
     def generate(self, latent, text, n_cand=1, max_new=None, do_sample=False, temperature=1.0,
                  top_k=0, top_p=1.0, repetition_penalty=1.0, seed=1234, seq_index_base=0,
-                 ignore_eos=False, forced=None, want_logits=0, sampler="philox"):
+                 ignore_eos=False, forced=None, want_logits=0, sampler="philox", typical_mass=None):
         """ref stream_generator.py:1106-1190 (sample_stream), driven by the ref's
         inference_speech bookkeeping (unified_voice.py:647-668).  Per step: forward -> logits[:, -1]
         -> processors (RepetitionPenalty over ALL input_ids incl. the dummy prompt ids 1 and 8192,
@@ -156,6 +156,7 @@ class OracleAR:
             lats.append(lat.float().clone())
             scores = logits.float()
             scores = apply_repetition_penalty(scores, ids, repetition_penalty)
+            scores = apply_typical(scores, typical_mass)      # custom processor, merged after the default ones (:659)
             if do_sample:
                 scores = apply_temperature(scores, temperature)
                 scores = apply_top_k(scores, top_k)
@@ -236,5 +237,25 @@ def apply_top_p(scores, p):
     cum = srt.softmax(dim=-1).cumsum(dim=-1)
     rem = cum <= (1 - p)
     rem[..., -1:] = False
+    rem = rem.scatter(1, idx, rem)
+    return scores.masked_fill(rem, float("-inf"))
+
+
+def apply_typical(scores, mass):
+    """Reference TypicalLogitsWarper (unified_voice.py:47-75; handed to generate() as a logits PROCESSOR by
+    inference_speech :659, so it runs after the repetition penalty and before temperature / top-k / top-p, in greedy
+    mode too): entropy of softmax(scores); shifted = |-log p - H|; ascending sort of shifted; cumulative
+    probability in that order; last_ind = #{cum < mass}; remove shifted > sorted_shifted[last_ind]."""
+    if mass is None or not (0.0 < mass < 1.0):
+        return scores
+    normalized = torch.log_softmax(scores, dim=-1)
+    p = torch.exp(normalized)
+    ent = -(normalized * p).nansum(-1, keepdim=True)
+    shifted = torch.abs((-normalized) - ent)
+    srt, idx = torch.sort(shifted, descending=False)
+    cum = scores.gather(-1, idx).softmax(dim=-1).cumsum(dim=-1)
+    last_ind = (cum < mass).sum(dim=1)
+    last_ind[last_ind < 0] = 0
+    rem = srt > srt.gather(1, last_ind.view(-1, 1))
     rem = rem.scatter(1, idx, rem)
     return scores.masked_fill(rem, float("-inf"))

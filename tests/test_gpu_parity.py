@@ -14,7 +14,8 @@ import pytest
 import torch
 
 from oracle import philox
-from oracle.uv_oracle import (OracleAR, apply_repetition_penalty, apply_temperature, apply_top_k, apply_top_p)
+from oracle.uv_oracle import (OracleAR, apply_repetition_penalty, apply_temperature, apply_top_k, apply_top_p,
+                              apply_typical)
 from oracle.weights import ARConfig, make_inputs, make_state_dict
 
 pytestmark = pytest.mark.gpu
@@ -461,4 +462,112 @@ def test_fixup_codes_epilogue_bit_exact(b200, golden_dir):
         m.fix_autoregressive_codes(torch.zeros(2, 8, dtype=torch.int32, device="cuda"))
     with pytest.raises(ValueError):                                      # len < 3: BAD_ARG from the C ABI
         m.fix_autoregressive_codes(torch.full((1, 2), 8193, dtype=torch.int64, device="cuda"))
+    m.close()
+
+
+def typical_row_is_stable(scores, mass, eps=3e-6):
+    """True when no token sits within fp32 distance of the typical threshold (shifted value or mass), so that the
+    reference's support set does not depend on how log_softmax was rounded.  float64."""
+    s = scores.double().numpy()
+    e = np.exp(s - s.max())
+    pr = e / e.sum()
+    cT = (pr * s).sum()
+    sh = np.abs(cT - s)
+    order = np.argsort(sh, kind="stable")
+    cs = np.cumsum(pr[order])
+    j = int((cs < mass).sum())                    # index of the threshold token in sorted order
+    if j >= len(cs) - 1:
+        return False
+    lo = cs[j - 1] if j > 0 else 0.0
+    gap_next = sh[order[j + 1]] - sh[order[j]]
+    gap_prev = sh[order[j]] - sh[order[j - 1]] if j > 0 else 1.0
+    return min(mass - lo, cs[j] - mass) > eps and min(gap_next, gap_prev) > eps * max(1.0, sh[order[j]])
+
+
+@pytest.mark.parametrize("kw", [dict(typical_mass=0.9, temperature=1.0, top_k=0, top_p=1.0),
+                                dict(typical_mass=0.5, temperature=0.8, top_k=0, top_p=0.8, repetition_penalty=2.0),
+                                dict(typical_mass=0.2, temperature=1.3, top_k=40, top_p=1.0),
+                                dict(typical_mass=0.99, temperature=0.7, top_k=50, top_p=0.9)])
+def test_typical_sampling_equals_reference_warper_on_device_logits(b200, kw):
+    """typical_sampling=True (reference unified_voice.py:47-75, :659): repetition penalty -> TypicalLogitsWarper ->
+    temperature -> top-k -> top-p -> multinomial on the DEVICE's logits vs the oracle chain (apply_typical is pinned
+    to the reference's own class by tests/test_oracle_golden.py).  Rows with a token inside fp32 distance of the
+    typical threshold are skipped (the reference's own answer there depends on log_softmax rounding)."""
+    kw = dict(kw)
+    mass = kw["typical_mass"]
+    m, o, cfg, lat, texts = make_small(b200, U=1, T=12, max_utts=1, max_seqs=24, max_new_tokens=16)
+    text = torch.stack(texts)
+    N, seed, base = 24, 99, 500
+    m._prefill(lat.cuda(), text.cuda(), N)
+    s = m._sampling(dict(do_sample=True, seed=seed, seq_index_base=base, **kw))
+    ids = torch.full((N, text.shape[1] + 4), 1, dtype=torch.long)
+    ids[:, -1] = cfg.start_mel_token
+    n_checked = n_rows = 0
+    for step in range(6):
+        lg = m.logits_debug().cpu()
+        if step == 0:
+            lg = lg.repeat_interleave(N, 0)
+        pre = apply_repetition_penalty(lg.clone(), ids, kw.get("repetition_penalty", 1.0))
+        sc = apply_typical(pre.clone(), mass)
+        sc = apply_top_p(apply_top_k(apply_temperature(sc, kw["temperature"]), kw["top_k"]), kw["top_p"])
+        out = torch.zeros(N, 1, dtype=torch.int64, device="cuda")
+        m._check(m.lib.tts_ar_step(m.handle, C.byref(s), 1, C.c_void_p(out.data_ptr()), C.c_void_p(0), C.c_void_p(0),
+                                   C.c_void_p(0), m._stream()), "step")
+        m.sync_stats()
+        out = out.cpu()[:, 0]
+        for r in range(N):
+            n_rows += 1
+            if not typical_row_is_stable(pre[r], mass):
+                continue
+            tok, margin = philox.multinomial_row(sc[r].numpy(), philox.uniform(seed, base + r, step))
+            assert torch.isfinite(sc[r, out[r]]), "device sampled a token outside the reference's typical support set"
+            if margin > 1e-5:
+                assert int(out[r]) == tok, (step, r, int(out[r]), tok, margin)
+                n_checked += 1
+        ids = torch.cat([ids, out[:, None]], 1)
+    print("typical: rows checked", n_checked, "of", n_rows)
+    assert n_checked > 0.5 * n_rows
+    m.close()
+
+
+def test_typical_sampling_greedy_and_cluster_kernel(b200):
+    """The typical warper is a logits processor, so it also filters the greedy argmax (the most likely token is NOT
+    always in the typical set).  Teacher-forced, 16 sequences -> the head-cluster kernel; the recorded choices equal
+    the oracle's argmax over the typical-filtered scores wherever the oracle's own top-2 gap exceeds the bf16 logits
+    tolerance."""
+    UV, Geo = b200
+    cfg = ARConfig(layers=2)
+    sd = make_state_dict(cfg, seed=7, attn_std=0.04)
+    sd["mel_head.weight"] = sd["mel_head.weight"] * 8.0
+    sd = bf16_weights(sd)
+    lat, texts = make_inputs(cfg, 1, [12], seed=9)
+    text = torch.stack(texts)
+    o = OracleAR(sd, cfg)
+    steps, N, mass = 12, 16, 0.3
+    ref = o.generate(lat, text, n_cand=N, max_new=steps, typical_mass=mass, repetition_penalty=2.0, want_logits=steps,
+                     ignore_eos=True)
+    m = UV(sd, Geo(layers=2), max_utts=1, max_seqs=N, max_text_len=16, max_new_tokens=32)
+    got, choice = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=N, max_generate_length=steps,
+                                     typical_sampling=True, typical_mass=mass, repetition_penalty=2.0,
+                                     forced_tokens=ref["codes"], return_choice=True, ignore_eos=True)
+    assert torch.equal(got.cpu(), ref["codes"])
+    ids = torch.full((N, 16), 1, dtype=torch.long)
+    ids[:, -1] = cfg.start_mel_token
+    n_ok = n_all = n_not_mode = 0
+    for k in range(steps):
+        hist = torch.cat([ids, ref["codes"][:, :k]], 1)
+        pre = apply_repetition_penalty(ref["logits"][k].clone(), hist, 2.0)
+        sc = apply_typical(pre.clone(), mass)
+        for r in range(N):
+            n_all += 1
+            if not typical_row_is_stable(pre[r], mass, eps=2e-2):      # bf16 logits move the threshold too
+                continue
+            top2 = torch.topk(sc[r], 2).values
+            if (top2[0] - top2[1]).item() / ref["logits"][k][r].abs().max().item() < BF16_REL:
+                continue
+            assert int(choice[r, k]) == int(sc[r].argmax()), (k, r)
+            n_ok += 1
+            n_not_mode += int(sc[r].argmax() != pre[r].argmax())
+    print("typical greedy: checked", n_ok, "of", n_all, "; argmax outside the typical set in", n_not_mode)
+    assert n_ok >= 0.3 * n_all
     m.close()

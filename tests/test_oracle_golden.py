@@ -127,3 +127,47 @@ def test_fixup_oracle_matches_the_executed_reference_lines(golden_dir):
         fixup_codes(row)
     fixed, first = fixup_codes(row, strict=False)
     assert np.array_equal(fixed, row) and first[0] == -1 and calm_trim(fixed) == 20
+
+
+def test_typical_warper_matches_the_reference_class(golden_dir):
+    """oracle.apply_typical vs tests/golden/typical.npz = the reference's own TypicalLogitsWarper
+    (unified_voice.py:47-75) run by oracle/make_golden_typical.py.  Support sets are bit-exact (same torch ops)."""
+    from oracle.uv_oracle import apply_typical
+    g = np.load(os.path.join(golden_dir, "typical.npz"))
+    logits = torch.from_numpy(g["logits"])
+    for mass in (0.9, 0.5, 0.2, 0.99):
+        got = torch.isfinite(apply_typical(logits.clone(), mass)).numpy()
+        assert np.array_equal(got, g[f"keep{int(mass * 100)}"]), mass
+    assert torch.equal(apply_typical(logits, None), logits) and torch.equal(apply_typical(logits, 1.0), logits)
+
+
+def test_typical_mass_rule_equals_reference_support(golden_dir):
+    """The device sampler keeps token i iff (probability mass of tokens with a strictly smaller
+    |s_i - E_p[s]|) < mass, with E_p[s] = smax + sum e (s - smax) / sum e: the reference's sort + cumsum rule without
+    the sort (csrc/ar_sample.cuh, pass -1).  Identical support sets on the reference's golden rows, evaluated in
+    float64; a token may differ only if its shifted value ties the threshold to 1e-6 (fp32 rounding of the
+    reference's log_softmax)."""
+    g = np.load(os.path.join(golden_dir, "typical.npz"))
+    logits = g["logits"].astype(np.float64)
+    for mass in (0.9, 0.5, 0.2, 0.99):
+        want = g[f"keep{int(mass * 100)}"]
+        for r in range(logits.shape[0]):
+            s = logits[r]
+            fin = np.isfinite(s)
+            e = np.where(fin, np.exp(s - s[fin].max()), 0.0)
+            cT = s[fin].max() + (e[fin] * (s[fin] - s[fin].max())).sum() / e.sum()
+            shifted = np.where(fin, np.abs(cT - np.where(fin, s, 0.0)), np.inf)
+            pr = e / e.sum()
+            order = np.argsort(shifted, kind="stable")
+            below = np.zeros_like(pr)
+            cs = np.cumsum(pr[order])
+            # mass of strictly smaller shifted values (ties share the same "below")
+            sh_sorted = shifted[order]
+            first_of_group = np.searchsorted(sh_sorted, sh_sorted, side="left")
+            below[order] = np.where(first_of_group > 0, cs[np.maximum(first_of_group - 1, 0)], 0.0)
+            got = (below < mass) & fin
+            diff = np.nonzero(got != want[r])[0]
+            if diff.size:
+                thr = shifted[want[r]].max()
+                assert np.all(np.abs(shifted[diff] - thr) < 1e-6 * max(1.0, thr)), (mass, r, diff[:5])
+                assert diff.size <= 2

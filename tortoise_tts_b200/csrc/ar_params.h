@@ -105,6 +105,7 @@ struct Params {
   // sampler config
   int do_sample, top_k, ignore_eos;
   float temperature, top_p, rep_penalty;
+  float typical_mass;            // TypicalLogitsWarper mass in (0,1); 0 = off
   unsigned long long seed;
   long long seq_index_base;
   int stop_token;

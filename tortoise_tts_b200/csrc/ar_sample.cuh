@@ -107,6 +107,7 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
   const uint32_t* seen = P.seen + (size_t)seq * P.seen_words;
   const float pen = P.rep_penalty;
   const bool use_temp = P.do_sample && P.temperature != 1.0f;
+  const bool typ = P.typical_mass > 0.f;            // reference TypicalLogitsWarper (unified_voice.py:47-75, :659)
 
   // scores = processors(logits): repetition penalty, then (sampling only) temperature; kept as keys in sk[]
   // The row is copied L2 -> shared memory asynchronously (one round trip for the whole row), then transformed in
@@ -121,41 +122,51 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
   for (int v = tid; v < V; v += kConsumerThreads) {
     float s = sc[v];
     if (pen != 1.0f && ((__ldcg(seen + (v >> 5)) >> (v & 31)) & 1u)) s = (s < 0.f) ? s * pen : s / pen;
-    if (use_temp) s = s / P.temperature;
+    if (use_temp && !typ) s = s / P.temperature;   // typical runs on the un-tempered scores: applied after it
     sk[v] = key_of(s);
     lmax = fmaxf(lmax, s);
     lmin = fminf(lmin, s);
   }
   block_maxmin(lmax, lmin, scratch);               // also orders the sk[] writes before the reads below
-  const float smax = lmax, smin = lmin;
-  const uint32_t kmax = key_of(smax);
+  float smax = lmax, smin = lmin;
+  uint32_t kmax = key_of(smax);
   prof_mark(P, c, 31);
 
   int token;
-  if (!P.do_sample) {
-    // HF greedy: argmax of the processed scores; first index on ties (torch.argmax)
-    int best = 0x7fffffff;
-#pragma unroll kSmpUnroll
-    for (int v = tid; v < V; v += kConsumerThreads)
-      if (sk[v] == kmax) best = min(best, v);
-    best = __reduce_min_sync(0xffffffffu, best);
-    consumer_sync();
-    if ((tid & 31) == 0) reinterpret_cast<int*>(scratch)[tid >> 5] = best;
-    consumer_sync();
-    int b2 = ((tid & 31) < kNW) ? reinterpret_cast<int*>(scratch)[tid & 31] : 0x7fffffff;
-    token = __reduce_min_sync(0xffffffffu, b2);
-  } else {
-    uint32_t kmin = key_of(-INFINITY);             // keep key >= kmin
+  uint32_t kmin = key_of(-INFINITY);               // keep key >= kmin
+  if (P.do_sample || typ) {
     int par = 0;
     float Z = 0.f;
     int n_keep = V;                                 // #{key >= kmin}
-    // pass 0 = top-k, pass 1 = softmax numerators + top-p.  One copy of the search code (the sampler runs once per
-    // step, so every instruction of it is an instruction-cache miss: loops are kept rolled on purpose).
+    // pass -1 = typical (only when asked for), pass 0 = top-k, pass 1 = softmax numerators + top-p.  One copy of the
+    // search code (the sampler runs once per step, so every instruction of it is an instruction-cache miss: loops are
+    // kept rolled on purpose).
 #pragma unroll 1
-    for (int pass = 0; pass < 2; ++pass) {
+    for (int pass = typ ? -1 : 0; pass < 2; ++pass) {
       const bool ones = pass == 0;
+      const bool tmode = pass < 0;
       float lim;
-      if (ones) {
+      float cT = 0.f, pmn = smin, pmx = smax;       // probe range of the keys being searched
+      if (tmode) {
+        // TypicalLogitsWarper: shifted_i = |-log p_i - H| = |(smax + S1/Z) - s_i| with e_i = exp(s_i - smax),
+        // Z = sum e_i, S1 = sum e_i (s_i - smax) (H = log Z - S1/Z).  Token i is kept iff the probability mass of the
+        // tokens with a strictly smaller shifted value is < mass: the top-p rule over the key -shifted.
+        float zl[2] = {0.f, 0.f};
+#pragma unroll 3
+        for (int v = tid; v < V; v += kConsumerThreads) {
+          const float d = key_to_float(sk[v]) - smax;
+          const float ex = expf(d);
+          ev[v] = ex;
+          zl[0] += ex;
+          zl[1] += (ex > 0.f) ? ex * d : 0.f;       // nansum: 0 * -inf is skipped
+        }
+        block_sum_k<2>(zl, rbuf + par * 48);
+        par ^= 1;
+        cT = smax + zl[1] / zl[0];
+        lim = P.typical_mass * zl[0];
+        pmx = 0.f;
+        pmn = -fmaxf(fabsf(cT - smax), fabsf(cT - smin));
+      } else if (ones) {
         if (!(P.top_k > 0 && P.top_k < V)) continue;
         lim = (float)P.top_k;                       // counts <= 8448 are exact in fp32
       } else {
@@ -179,7 +190,7 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
         lim = P.top_p * Z;
       }
       // smallest T in [lo, hi] with weight{key > T} < lim.  pred(hi) holds: nothing lies above the maximum.
-      uint32_t lo = kmin, hi = kmax;
+      uint32_t lo = kmin, hi = tmode ? key_of(0.f) : kmax;
       int n_lo = n_keep, n_hi = 0;                  // #{key >= lo}, #{key > hi}
       float m_hi = 0.f;                             // weight{key > hi}
       bool first = true;
@@ -188,7 +199,8 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
           // gather the candidates (order arbitrary: sorted next), every warp finishes redundantly
 #pragma unroll 3
           for (int v = tid; v < V; v += kConsumerThreads) {
-            const uint32_t k = sk[v];
+            uint32_t k = sk[v];
+            if (tmode) k = key_of(-fabsf(cT - key_to_float(k)));
             if (k >= lo && k <= hi) {
               const int p = atomicAdd(scnt, 1);
               if (p < 32) slist[p] = ((unsigned long long)k << 32) | __float_as_uint(ones ? 1.f : ev[v]);
@@ -215,12 +227,12 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
         // maximum, where the edge almost always is); quarters of the key interval when those degenerate
         uint32_t t[3];
         {
-          const float fl = fmaxf(key_to_float(lo), smin), fh = key_to_float(hi);
+          const float fl = fmaxf(key_to_float(lo), pmn), fh = key_to_float(hi);
           bool ok = true;
 #pragma unroll
           for (int j = 0; j < 3; ++j) {
             float pj = fl + (fh - fl) * (0.25f * (j + 1));
-            if (first) pj = fmaxf(pj, smax - (j == 0 ? 16.f : j == 1 ? 4.f : 1.f));
+            if (first) pj = fmaxf(pj, pmx - (j == 0 ? 16.f : j == 1 ? 4.f : 1.f));
             t[j] = key_of(pj);
             ok = ok && (fabsf(pj) <= 3.0e38f);
           }
@@ -236,7 +248,8 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
         int cn[3] = {0, 0, 0};                      // #{key > t[j]}
 #pragma unroll 3
         for (int v = tid; v < V; v += kConsumerThreads) {
-          const uint32_t k = sk[v];
+          uint32_t k = sk[v];
+          if (tmode) k = key_of(-fabsf(cT - key_to_float(k)));
           const float wgt = ones ? 1.f : ev[v];
 #pragma unroll
           for (int j = 0; j < 3; ++j) {
@@ -278,9 +291,51 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
         else if (ms[2] < lim) { lo = t[1] + 1u; n_lo = cn[1]; hi = t[2]; m_hi = ms[2]; n_hi = cn[2]; }
         else { lo = t[2] + 1u; n_lo = cn[2]; }
       }
+      if (tmode) {
+        // apply the typical filter (removed tokens get the key of -inf), then the deferred temperature; the maximum,
+        // minimum and count of the survivors restart the top-k / top-p searches (and the greedy argmax)
+        float mx = -INFINITY, mn = INFINITY;
+        float zl[2] = {0.f, 0.f};
+#pragma unroll 3
+        for (int v = tid; v < V; v += kConsumerThreads) {
+          float sv = key_to_float(sk[v]);
+          if (key_of(-fabsf(cT - sv)) >= lo) {
+            if (use_temp) sv = sv / P.temperature;
+            sk[v] = key_of(sv);
+            mx = fmaxf(mx, sv);
+            mn = fminf(mn, sv);
+            zl[1] += 1.f;
+          } else {
+            sk[v] = key_of(-INFINITY);
+          }
+        }
+        block_sum_k<2>(zl, rbuf + par * 48);
+        par ^= 1;
+        block_maxmin(mx, mn, scratch);
+        smax = mx; smin = mn;
+        kmax = key_of(smax);
+        kmin = key_of(smin);
+        n_keep = (int)zl[1];
+        if (!P.do_sample) break;
+        continue;
+      }
       kmin = lo;
       n_keep = n_lo;                                // upper bound is all the next pass needs
     }
+  }
+  if (!P.do_sample) {
+    // HF greedy: argmax of the processed scores; first index on ties (torch.argmax)
+    int best = 0x7fffffff;
+#pragma unroll kSmpUnroll
+    for (int v = tid; v < V; v += kConsumerThreads)
+      if (sk[v] == kmax) best = min(best, v);
+    best = __reduce_min_sync(0xffffffffu, best);
+    consumer_sync();
+    if ((tid & 31) == 0) reinterpret_cast<int*>(scratch)[tid >> 5] = best;
+    consumer_sync();
+    int b2 = ((tid & 31) < kNW) ? reinterpret_cast<int*>(scratch)[tid & 31] : 0x7fffffff;
+    token = __reduce_min_sync(0xffffffffu, b2);
+  } else {
     consumer_sync();                               // ev[] complete before the vocabulary-ordered reads
     prof_mark(P, c, 33);
     // ---- multinomial: inverse CDF in vocabulary order (thread t owns tokens 33t .. 33t+32) ----

@@ -204,6 +204,7 @@ static int run_steps(TtsArHandle* h, const TtsArSampling* s, int n_steps, bool s
   P.first_step_from_prefill = h->first_step_pending ? 1 : 0;
   P.do_sample = s->do_sample; P.top_k = s->top_k; P.ignore_eos = s->ignore_eos;
   P.temperature = s->temperature; P.top_p = s->top_p; P.rep_penalty = s->repetition_penalty;
+  P.typical_mass = (s->typical_mass > 0.f && s->typical_mass < 1.f) ? s->typical_mass : 0.f;
   P.seed = s->seed; P.seq_index_base = s->seq_index_base;
   P.out_codes = out_codes; P.out_stride = n_steps; P.out_latents = out_latents; P.forced = forced; P.out_choice = out_choice;
   int rc = launch(h, P, st, h->use_cluster && h->n_seqs <= kDecRows);

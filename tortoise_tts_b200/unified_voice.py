@@ -157,6 +157,9 @@ class UnifiedVoiceB200:
         s.seed = int(kw.pop("seed", 0))              # reference generate(seed=0), stream_generator.py:223
         s.seq_index_base = int(kw.pop("seq_index_base", 0))
         s.ignore_eos = 1 if kw.pop("ignore_eos", False) else 0
+        # reference: LogitsProcessorList([TypicalLogitsWarper(mass=typical_mass)]) if typical_sampling (:659)
+        tm = kw.pop("typical_mass", None)
+        s.typical_mass = 0.0 if tm is None else float(tm)
         for ignored in ("length_penalty", "output_attentions", "output_hidden_states", "return_dict_in_generate",
                         "logits_processor", "bos_token_id", "pad_token_id", "eos_token_id", "use_cache"):
             kw.pop(ignored, None)
@@ -230,7 +233,9 @@ class UnifiedVoiceB200:
         if input_tokens is not None:
             raise NotImplementedError("input_tokens (continuation) is not supported")
         if typical_sampling:
-            raise NotImplementedError("typical_sampling is not supported yet (no reference caller sets it)")
+            if not 0.0 < float(typical_mass) < 1.0:
+                raise ValueError("typical_mass must be in (0, 1)")
+            hf_generate_kwargs = dict(hf_generate_kwargs, typical_mass=typical_mass)
         s = self._sampling(hf_generate_kwargs)
         max_new = (self.max_mel_tokens - 1) if max_generate_length is None else int(max_generate_length)
         U, _ = self._prefill(speech_conditioning_latent, text_inputs, num_return_sequences, text_lengths)
