@@ -7,6 +7,7 @@
 namespace tts {
 
 constexpr int kMaxSlots = 12;
+constexpr int kLnSplitMinRows = 16;   // interpreter: LayerNorm as its own grid-wide phase above this many rows
 
 struct Ctrl {
   uint64_t full[kMaxSlots];    // producer -> consumers: chunk landed (tx-count barrier)
@@ -322,6 +323,28 @@ __device__ void ln_rows_to_smem(const Params& P, const Instr& ins, uint8_t* a_rm
     } else if (r1 < mt_count * 16) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) *reinterpret_cast<uint2*>(d1 + (128 * j + 4 * lane) * 2) = make_uint2(0u, 0u);
+    }
+  }
+}
+
+// ---- LayerNorm of ALL rows of an ln_1 / ln_2 stage, once, grid-wide (interpreter, more than 16 rows) ---------------
+// Warp (cta, w) normalises rows gw, gw + 8 G, ... and stores them as bf16 in mma A-fragment order (P.xn); after the grid
+// barrier that follows, the GEMM reads its A fragments from L2 exactly like the attn.c_proj stage reads the context.
+// Without this every CTA re-normalises all rows for its own column slice: 148 x the loads and the arithmetic.
+__device__ __forceinline__ bool ln_split_active(const Params& P) { return P.xn != nullptr && P.n_rows > kLnSplitMinRows; }
+
+static __device__ void ln_rows_to_global(const Params& P, const Instr& ins, const float* g, const float* b) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int row = w * P.G + blockIdx.x; row < P.n_rows; row += kNW * P.G) {     // CTA-major: one row per CTA first
+    float4 v[8];
+    ln_load_row(P, ins, P.x, row, lane, v);
+    ln_normalise(v, g, b, lane);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int col = 128 * j + 4 * lane;
+      __nv_bfloat16* d = P.xn + afrag_elem_offset(row, col, kD);
+      *reinterpret_cast<uint32_t*>(d) = pack_bf16x2(v[j].x, v[j].y);
+      *reinterpret_cast<uint32_t*>(P.xn + afrag_elem_offset(row, col + 2, kD)) = pack_bf16x2(v[j].z, v[j].w);
     }
   }
 }

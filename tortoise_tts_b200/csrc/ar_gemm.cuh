@@ -91,7 +91,8 @@ __device__ void gemm_tiles(const Params& P, const Instr& ins, const Smem& sm, Pi
   GemmDesc gd;
   gemm_desc(P, ins, gd);
   const int KQ = gd.K / kChunkK;
-  const bool a_from_smem = (ins.op == OP_LN_QKV || ins.op == OP_LN_FC || ins.op == OP_HEAD);
+  const bool ln_split = ln_split_active(P) && (ins.op == OP_LN_QKV || ins.op == OP_LN_FC);
+  const bool a_from_smem = !ln_split && (ins.op == OP_LN_QKV || ins.op == OP_LN_FC || ins.op == OP_HEAD);
 
   // ---- A operand ----
   if (a_from_smem && !a_staged) {
@@ -109,7 +110,7 @@ __device__ void gemm_tiles(const Params& P, const Instr& ins, const Smem& sm, Pi
                              (uint32_t)((lane >> 4) * 16);
   const uint4* a_gl = nullptr;
   if (!a_from_smem) {
-    const __nv_bfloat16* base = (ins.op == OP_PROJ) ? P.ctx : P.hbuf;
+    const __nv_bfloat16* base = ln_split ? P.xn : (ins.op == OP_PROJ) ? P.ctx : P.hbuf;
     a_gl = reinterpret_cast<const uint4*>(base) + ((size_t)((ins.row0 >> 4) + mt) * (gd.K >> 4)) * 32 + lane;
   }
 

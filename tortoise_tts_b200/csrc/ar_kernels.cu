@@ -62,6 +62,13 @@ __global__ void __launch_bounds__(kThreads, 1) ar_program_kernel(const __grid_co
         case OP_LN_FC:
         case OP_PROJ2:
         case OP_HEAD: {
+          if ((ins.op == OP_LN_QKV || ins.op == OP_LN_FC) && ins.row0 == 0 && ln_split_active(P)) {
+            const float* fp = layer_f(P, ins.layer);
+            if (ins.op == OP_LN_QKV) ln_rows_to_global(P, ins, fp + kFOffLn1g, fp + kFOffLn1b);
+            else ln_rows_to_global(P, ins, fp + kFOffLn2g, fp + kFOffLn2b);
+            alive = grid_barrier(P, c, epoch);
+            if (!alive) break;
+          }
           const int mt = (ins.nrows + 15) >> 4;
           if (mt <= 1) gemm_stage<1>(P, ins, sm, pipe);
           else if (mt == 2) gemm_stage<2>(P, ins, sm, pipe);

@@ -77,6 +77,8 @@ struct Params {
   float* q;              // [rows][1024] query, pre-scaled by 1/sqrt(64)
   __nv_bfloat16* ctx;    // A-fragment layout, K = 1024
   __nv_bfloat16* hbuf;   // A-fragment layout, K = 4096
+  __nv_bfloat16* xn;     // A-fragment layout, K = 1024: LayerNorm'd rows of the current ln_1 / ln_2 stage when more than 16
+                         //   rows run through the interpreter (normalised ONCE, grid-wide, instead of by every CTA); nullable
   float* logits;         // [logit rows][v_stride]
   float* cur_latent;     // [logit rows][1024] final_norm(ln_f(x)) of the rows fed to the head
   // KV cache

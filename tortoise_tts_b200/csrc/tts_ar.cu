@@ -109,6 +109,7 @@ static int create_impl(TtsArHandle* h) {
   DALLOC(h, h->d_q, (size_t)h->rows_cap * kD);
   DALLOC(h, h->d_y, (size_t)kDecRows * kD);
   DALLOC(h, h->d_ctx, (size_t)h->rows_cap * kD);
+  DALLOC(h, h->d_xn, (size_t)h->rows_cap * kD);
   DALLOC(h, h->d_h, (size_t)h->rows_cap * kD4);
   DALLOC(h, h->d_logits, (size_t)h->logit_rows_cap * h->v_stride);
   DALLOC(h, h->d_cur_latent, (size_t)h->logit_rows_cap * kD);

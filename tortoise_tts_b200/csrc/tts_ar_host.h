@@ -40,7 +40,7 @@ struct TtsArHandle {
   long long* d_y = nullptr;            // cluster decode kernel: attention-block accumulator [16][1024]
   bool use_cluster = false;         // 16 clusters of 8 CTAs can be co-resident (checked at create)
   float *d_x = nullptr, *d_q = nullptr, *d_logits = nullptr, *d_cur_latent = nullptr, *d_part = nullptr;
-  __nv_bfloat16 *d_ctx = nullptr, *d_h = nullptr, *d_kv = nullptr;
+  __nv_bfloat16 *d_ctx = nullptr, *d_h = nullptr, *d_kv = nullptr, *d_xn = nullptr;
   int *d_prefix_pt = nullptr, *d_priv_pt = nullptr, *d_utt_plen = nullptr;
   int *d_pf_row_utt = nullptr, *d_pf_row_pos = nullptr, *d_head_rows = nullptr, *d_latent_dst = nullptr;
   int *d_seq_utt = nullptr, *d_seq_pos = nullptr;

@@ -24,6 +24,10 @@ void fill_common_params(TtsArHandle* h, Params& P) {
   P.lnf_g = h->d_lnf_g; P.lnf_b = h->d_lnf_b; P.fn_g = h->d_fn_g; P.fn_b = h->d_fn_b;
   P.mel_emb = h->d_mel_emb; P.mel_pos = h->d_mel_pos;
   P.x = h->d_x; P.q = h->d_q; P.ctx = h->d_ctx; P.hbuf = h->d_h;
+  {
+    static const bool fused_ln = getenv("TTS_AR_LN_FUSED") != nullptr;   // bring-up A/B: every CTA normalises all rows itself
+    P.xn = fused_ln ? nullptr : h->d_xn;
+  }
   P.logits = h->d_logits; P.cur_latent = h->d_cur_latent;
   P.kv = h->d_kv; P.n_pages = h->n_pages;
   P.prefix_pt = h->d_prefix_pt; P.priv_pt = h->d_priv_pt; P.utt_plen = h->d_utt_plen;
