@@ -1,5 +1,6 @@
 // ar_kernels.cu -- the persistent interpreter kernel (one CTA per SM, cooperative launch) and the small
 // setup kernels (weight repacking, prompt embedding, sampler-state reset).
+#include <algorithm>
 #include "ar_gemm.cuh"
 #include "ar_attn.cuh"
 #include "ar_sample.cuh"
@@ -213,7 +214,12 @@ __global__ void reset_sampler_kernel(int n_seqs, int seen_words, uint32_t* seen,
     row_pos[i] = -1;
   }
   if (i < n_cnt) attn_cnt[i] = 0;
-  if (i == 0) *n_active = n_seqs;
+  if (i == 0) {
+    n_active[0] = n_seqs;
+    // 16-sequence groups of a 17..32-sequence batch run as consecutive head-cluster launches (tts_ar_run.cu run_steps)
+    n_active[1] = min(n_seqs, kDecRows);
+    n_active[2] = max(0, min(n_seqs - kDecRows, kDecRows));
+  }
 }
 
 void launch_reset_sampler(int n_seqs, int seen_words, uint32_t* seen, int* finished, int* gen_count, int* row_pos,
@@ -267,6 +273,15 @@ __global__ void fixup_codes_kernel(long long* __restrict__ codes, int len, int s
 void launch_fixup_codes(long long* codes, int rows, int len, int stride, int stop, int calm, int* first_stop, int* trim,
                         cudaStream_t st) {
   fixup_codes_kernel<<<rows, 128, 0, st>>>(codes, len, stride, stop, calm, first_stop, trim);
+}
+
+__global__ void fill_i64_kernel(long long* p, size_t n, long long v) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
+}
+
+void launch_fill_i64(long long* p, size_t n, long long v, cudaStream_t st) {
+  const int blocks = (int)std::min<size_t>((n + 255) / 256, 1024);
+  if (n) fill_i64_kernel<<<blocks, 256, 0, st>>>(p, n, v);
 }
 
 cudaError_t launch_program(const Params& P, int smem_bytes, cudaStream_t st) {

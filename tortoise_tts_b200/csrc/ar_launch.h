@@ -27,6 +27,7 @@ void launch_fixup_codes(long long* codes, int rows, int len, int stride, int sto
                         cudaStream_t st);
 void launch_reset_sampler(int n_seqs, int seen_words, uint32_t* seen, int* finished, int* gen_count, int* row_pos,
                           int* n_active, int start_mel, int* attn_cnt, int n_cnt, cudaStream_t st);
+void launch_fill_i64(long long* p, size_t n, long long v, cudaStream_t st);
 cudaError_t launch_program(const Params& P, int smem_bytes, cudaStream_t st);
 int program_max_ctas_per_sm(int smem_bytes);
 // head-cluster decode kernel (ar_decode.cu)

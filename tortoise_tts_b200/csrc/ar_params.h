@@ -81,6 +81,8 @@ struct Params {
                          //   rows run through the interpreter (normalised ONCE, grid-wide, instead of by every CTA); nullable
   float* logits;         // [logit rows][v_stride]
   float* cur_latent;     // [logit rows][1024] final_norm(ln_f(x)) of the rows fed to the head
+  const float* logits_pf;      // prompt-pass logits / latents, row = utterance: what the first SAMPLE after a prefill reads
+  const float* cur_latent_pf;  //   (== logits / cur_latent unless the launch covers a 16-sequence group of a larger batch)
   // KV cache
   __nv_bfloat16* kv;     // page pool (layout.h kv_row_offset)
   int n_pages;

@@ -102,8 +102,9 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
     }
     return;
   }
-  const int lrow = (P.first_step_from_prefill && step_col == 0) ? P.seq_utt[seq] : seq;
-  const float* lg = P.logits + (size_t)lrow * P.v_stride;
+  const bool from_pf = P.first_step_from_prefill && step_col == 0;
+  const int lrow = from_pf ? P.seq_utt[seq] : seq;
+  const float* lg = (from_pf ? P.logits_pf : P.logits) + (size_t)lrow * P.v_stride;
   const uint32_t* seen = P.seen + (size_t)seq * P.seen_words;
   const float pen = P.rep_penalty;
   const bool use_temp = P.do_sample && P.temperature != 1.0f;
@@ -413,7 +414,7 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
     }
   }
   if (P.out_latents) {   // final_norm(hidden) of the forward pass that produced these logits (:1172)
-    const float* src = P.cur_latent + (size_t)lrow * kD;
+    const float* src = (from_pf ? P.cur_latent_pf : P.cur_latent) + (size_t)lrow * kD;
     float* dst = P.out_latents + oidx * kD;
     for (int i = tid; i < kD / 4; i += kConsumerThreads)
       reinterpret_cast<float4*>(dst)[i] = ld_cg_f4(src + 4 * i);

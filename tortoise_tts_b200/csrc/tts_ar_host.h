@@ -56,6 +56,7 @@ struct TtsArHandle {
   float* d_in_latent = nullptr;
   int* d_in_text = nullptr;
   long long* d_out_codes = nullptr;
+  bool grouped = false;          // last run_steps ran 16-sequence groups as consecutive head-cluster launches
   int *h_pinned_i = nullptr;     // pinned int scratch: [0]=steps_done [1]=watchdog
   long long* h_pinned_codes = nullptr;
   float* h_pinned_latent = nullptr;

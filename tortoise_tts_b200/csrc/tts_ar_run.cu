@@ -29,6 +29,7 @@ void fill_common_params(TtsArHandle* h, Params& P) {
     P.xn = fused_ln ? nullptr : h->d_xn;
   }
   P.logits = h->d_logits; P.cur_latent = h->d_cur_latent;
+  P.logits_pf = h->d_logits; P.cur_latent_pf = h->d_cur_latent;
   P.kv = h->d_kv; P.n_pages = h->n_pages;
   P.prefix_pt = h->d_prefix_pt; P.priv_pt = h->d_priv_pt; P.utt_plen = h->d_utt_plen;
   P.head_rows = h->d_head_rows;
@@ -211,7 +212,40 @@ static int run_steps(TtsArHandle* h, const TtsArSampling* s, int n_steps, bool s
   P.typical_mass = (s->typical_mass > 0.f && s->typical_mass < 1.f) ? s->typical_mass : 0.f;
   P.seed = s->seed; P.seq_index_base = s->seq_index_base;
   P.out_codes = out_codes; P.out_stride = n_steps; P.out_latents = out_latents; P.forced = forced; P.out_choice = out_choice;
-  int rc = launch(h, P, st, h->use_cluster && h->n_seqs <= kDecRows);
+  // 17..32 sequences: two consecutive launches of the 16-row head-cluster kernel (670 us/step each) beat one pass of the
+  // interpreter over 32 rows (1630 us/step).  Every per-sequence array is a pointer offset; sequences are independent and
+  // the Philox key is the global sequence index, so the result is bit-identical to two separate 16-candidate calls.
+  static const bool no_groups = getenv("TTS_AR_NO_GROUPS") != nullptr;
+  h->grouped = h->use_cluster && !no_groups && h->n_seqs > kDecRows && h->n_seqs <= 2 * kDecRows;
+  int rc = 0;
+  if (h->grouped) {
+    const int stash = 2 * kDecRows;            // logit rows [32, 32 + n_utt): the prompt-pass rows, kept for group 1
+    if (h->first_step_pending) {
+      TTS_CUDA(h, cudaMemcpyAsync(h->d_logits + (size_t)stash * h->v_stride, h->d_logits, sizeof(float) * h->n_utt * h->v_stride,
+                                  cudaMemcpyDeviceToDevice, st));
+      TTS_CUDA(h, cudaMemcpyAsync(h->d_cur_latent + (size_t)stash * kD, h->d_cur_latent, sizeof(float) * h->n_utt * kD,
+                                  cudaMemcpyDeviceToDevice, st));
+    }
+    for (int g = 0; g * kDecRows < h->n_seqs && !rc; ++g) {
+      const int s0 = g * kDecRows, cnt = std::min(kDecRows, h->n_seqs - s0);
+      Params Q = P;
+      Q.n_rows = Q.n_head_rows = Q.n_seqs = cnt;
+      Q.x += (size_t)s0 * kD; Q.q += (size_t)s0 * kD;
+      Q.logits += (size_t)s0 * h->v_stride; Q.cur_latent += (size_t)s0 * kD;
+      Q.logits_pf = h->d_logits + (size_t)stash * h->v_stride; Q.cur_latent_pf = h->d_cur_latent + (size_t)stash * kD;
+      Q.row_utt += s0; Q.row_pos += s0; Q.seq_utt += s0; Q.priv_pt += (size_t)s0 * kMaxPagesPerSeg;
+      Q.finished += s0; Q.gen_count += s0; Q.seen += (size_t)s0 * h->seen_words;
+      Q.n_active = h->d_n_active + 1 + g; Q.steps_done = h->d_steps_done + 1 + g;
+      Q.seq_index_base += s0;
+      Q.out_codes += (size_t)s0 * n_steps;
+      if (Q.out_latents) Q.out_latents += (size_t)s0 * n_steps * kD;
+      if (Q.forced) Q.forced += (size_t)s0 * n_steps;
+      if (Q.out_choice) Q.out_choice += (size_t)s0 * n_steps;
+      rc = launch(h, Q, st, true);
+    }
+  } else {
+    rc = launch(h, P, st, h->use_cluster && h->n_seqs <= kDecRows);
+  }
   if (rc) return rc;
   // SURVEY.md 8(d) algorithmic bytes, assuming every sequence stays live (exact under ignore_eos)
   const double W = 2.0 * ((double)c.n_layers * 12596224.0 + 4096.0 + (double)c.n_mel_codes * (kD + 1));
@@ -263,7 +297,15 @@ extern "C" int tts_ar_sync_result(TtsArHandle* h, TtsArStats* out, void* stream)
   TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[0], h->d_steps_done, sizeof(int), cudaMemcpyDeviceToHost, st));
   TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[1], h->d_watchdog, sizeof(int), cudaMemcpyDeviceToHost, st));
   TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[2], h->d_n_active, sizeof(int), cudaMemcpyDeviceToHost, st));
+  if (h->grouped) {   // per-group counters: the call ran until its slowest group finished
+    TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[4], h->d_steps_done + 1, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[6], h->d_n_active + 1, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+  }
   TTS_CUDA(h, cudaStreamSynchronize(st));
+  if (h->grouped) {
+    h->h_pinned_i[0] = std::max(h->h_pinned_i[4], h->h_pinned_i[5]);
+    h->h_pinned_i[2] = h->h_pinned_i[6] + h->h_pinned_i[7];
+  }
   memset(out, 0, sizeof(*out));
   out->struct_size = (int)sizeof(TtsArStats);
   out->steps_run = h->h_pinned_i[0];
@@ -373,6 +415,7 @@ extern "C" int tts_ar_inference_speech_host(TtsArHandle* h, const float* latent_
   TTS_CUDA(h, cudaMemcpyAsync(h->d_in_text, h->h_pinned_text, nb_txt, cudaMemcpyHostToDevice, st));
   rc = tts_ar_prefill(h, h->d_in_latent, h->d_in_text, text_stride, text_len, n_utt, n_cand, st);
   if (rc) return rc;
+  launch_fill_i64((long long*)h->d_out_codes, (size_t)n_utt * n_cand * max_new, c.stop_mel_token, st);   // columns a group that finished early never writes
   rc = tts_ar_generate(h, s, max_new, (int64_t*)h->d_out_codes, nullptr, nullptr, nullptr, st);
   if (rc) return rc;
   const size_t nb_out = sizeof(long long) * (size_t)h->n_seqs * max_new;
