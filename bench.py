@@ -30,7 +30,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-N_CAND = 16
+N_CAND = int(os.environ.get("TTS_BENCH_CANDIDATES", "16"))   # 32 = the per-GPU share of C3 (256 candidates over 8 GPUs); default = C2
 TEXT_LEN = 64
 MAX_NEW = int(os.environ.get("TTS_BENCH_MAX_NEW", "500"))   # override ONLY for short ncu captures (not a bench value)
 SAMPLING = dict(do_sample=True, top_p=0.8, temperature=0.8, top_k=0, repetition_penalty=1.0, seed=1234)
@@ -172,7 +172,7 @@ def run_reference(args):
 
 
 def workload_config(n_gpus):
-    return {"workload": "C2: UnifiedVoice AR (30 layers, d=1024, 16 heads, 8194 mel codes) bf16, 1 utterance, "
+    return {"workload": ("C2" if N_CAND == 16 else f"C3 share ({N_CAND} candidates per GPU)") + ": UnifiedVoice AR (30 layers, d=1024, 16 heads, 8194 mel codes) bf16, 1 utterance, "
                         f"{TEXT_LEN} text tokens, {N_CAND} candidates per GPU, top_p=0.8 temperature=0.8, "
                         f"{MAX_NEW} mel tokens (stop ignored), random-init weights seed 0",
             "candidates_per_gpu": N_CAND, "global_candidates": N_CAND * n_gpus, "max_new_tokens": MAX_NEW,
