@@ -264,3 +264,40 @@ def test_threshold_search_keeps_the_hf_support_set(std, top_k, top_p):
             cum_excl[order] = np.cumsum(p[order]) - p[order]
             assert np.all(np.abs(cum_excl[diff] - top_p) < 1e-4), (diff[:5], cum_excl[diff][:5])
         assert rounds <= 16, rounds
+
+
+@pytest.mark.parametrize("std,mass", [(1.0, 0.9), (2.5, 0.5), (6.0, 0.2), (0.3, 0.99), (2.5, 0.9)])
+def test_threshold_search_keeps_the_typical_support_set(std, mass):
+    """Pass -1 of the device sampler (csrc/ar_sample.cuh): the same search over the key -|s - E_p[s]| with weight
+    exp(s - max) and limit mass * Z selects the support of the reference's TypicalLogitsWarper
+    (oracle.apply_typical, pinned to the reference's own class by tests/test_oracle_golden.py).  fp32 throughout, as
+    on the device; tokens may differ only where |shifted - threshold| or the cumulative mass is within fp32 rounding."""
+    from oracle.uv_oracle import apply_typical
+    f32 = np.float32
+    rng = np.random.default_rng(int(std * 10) + int(mass * 100))
+    V = 8194
+    for trial in range(3):
+        sc = rng.normal(0, std, V).astype(np.float32)
+        smax, smin = sc.max(), sc.min()
+        d = (sc - smax).astype(np.float32)
+        e = np.exp(d).astype(np.float32)
+        Z = e.sum(dtype=np.float32)
+        cT = f32(smax + f32((e * d).sum(dtype=np.float32) / Z))
+        tk = _keys((-np.abs(cT - sc)).astype(np.float32))
+        lo0 = int(_keys(np.array([-np.inf], np.float32))[0])
+        pmn = f32(-max(abs(cT - smax), abs(cT - smin)))
+        T, rounds = _threshold_search(tk, e, f32(mass) * Z, lo0, V, pmn, f32(0.0))
+        mine = tk >= T
+        ref = torch.isfinite(apply_typical(torch.from_numpy(sc)[None], mass)[0]).numpy()
+        diff = np.nonzero(mine != ref)[0]
+        if len(diff):
+            s64 = sc.astype(np.float64)
+            p = np.exp(s64 - s64.max()); p /= p.sum()
+            sh = np.abs((p * s64).sum() - s64)
+            thr = sh[ref].max()
+            order = np.argsort(sh, kind="stable")
+            cum = np.cumsum(p[order])
+            j = int((cum < mass).sum())
+            near_mass = min(abs(cum[j] - mass), abs((cum[j - 1] if j else 0.0) - mass)) < 1e-5
+            assert len(diff) <= 2 and (near_mass or np.all(np.abs(sh[diff] - thr) < 1e-5 * max(1.0, thr))), (diff[:5], sh[diff][:5], thr)
+        assert mine.sum() >= 1 and rounds <= 16, rounds
