@@ -607,3 +607,34 @@ def test_32_sequences_run_as_two_head_cluster_groups_bit_exact(b200):
     assert torch.equal(h, whole)
     # and the interpreter (one 24-row pass) draws the same tokens up to bf16 reduction order: same support, mostly equal
     m.close()
+
+
+def test_dense_pass_tiled_attention_matches_oracle_and_row_path(b200, monkeypatch):
+    """Prompt-shaped passes with >= 1184 rows run their causal attention as 16-row mma tiles (csrc/ar_attn.cuh
+    attn_tile16; below that one decode-shaped unit per (row, head)).  The latent re-forward (unified_voice.py:544-600)
+    of 4 sequences x 317 positions crosses the threshold: vs the fp32 oracle at the bf16 tolerance, and vs the row path
+    (TTS_AR_DBG=2) of the same library.  317 is not a multiple of 16, so tiles that straddle two sequences (the per-row
+    fallback inside the tiled path) are exercised as well."""
+    UV, Geo = b200
+    cfg = ARConfig(layers=2)
+    sd = bf16_weights(make_state_dict(cfg, seed=7, attn_std=0.04))
+    lat, texts = make_inputs(cfg, 4, [12] * 4, seed=9)
+    text = torch.stack(texts)
+    M = 300
+    g = torch.Generator().manual_seed(5)
+    codes = torch.randint(0, 8192, (4, M), generator=g)
+    o = OracleAR(sd, cfg)
+    want = o.forward_latents(lat, text, codes)
+    m = UV(sd, Geo(layers=2), max_utts=4, max_seqs=4, max_text_len=16, max_new_tokens=M + 4)
+    args = (lat.cuda(), text.cuda(), torch.full((4,), 12), codes.cuda(), torch.full((4,), M * 1024))
+    monkeypatch.delenv("TTS_AR_DBG", raising=False)
+    tiled = m.forward(*args, return_latent=True, clip_inputs=False).cpu()
+    monkeypatch.setenv("TTS_AR_DBG", "2")
+    rows = m.forward(*args, return_latent=True, clip_inputs=False).cpu()
+    monkeypatch.delenv("TTS_AR_DBG")
+    assert tiled.shape == (4, M, 1024)
+    e_t, e_r, e_tr = rel(tiled, want), rel(rows, want), rel(tiled, rows)
+    print(f"dense attention: tiled vs oracle {e_t:.3e}, row path vs oracle {e_r:.3e}, tiled vs row path {e_tr:.3e}")
+    assert e_t < BF16_REL and e_r < BF16_REL and e_tr < BF16_REL
+    assert not torch.equal(tiled, rows)          # the two paths really are different code
+    m.close()

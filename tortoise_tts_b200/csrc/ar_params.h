@@ -134,7 +134,7 @@ struct Params {
   int n_steps;
   unsigned long long* prof;   // nullable: CTA 0 stage timestamps (ns) of step prof_step: [2*pc] before / [2*pc+1] after the barrier
   int prof_step;
-  int dbg_flags;         // bring-up A/B switches (TTS_AR_DBG): bit 0 = per-CTA LayerNorm instead of the cluster-cooperative one
+  int dbg_flags;         // bring-up A/B switches (TTS_AR_DBG): bit 0 = per-CTA LayerNorm instead of the cluster-cooperative one; bit 1 = prompt-pass attention as one decode-shaped unit per (row, head) instead of 16-row mma tiles; bit 2 = 16-row tiles whatever the row count
   int skip_last_model;   // generate(): the model is not run after the last sampled token
 };
 

@@ -58,12 +58,12 @@ static int launch(TtsArHandle* h, Params& P, cudaStream_t st, bool cluster = fal
   if (P.n_slots < 2) return fail(h, TTS_AR_ERR_DEVICE, "not enough shared memory for the weight ring");
   TTS_CUDA(h, cudaMemsetAsync(h->d_bar, 0, sizeof(unsigned int), st));
   cudaError_t e;
+  if (const char* e = getenv("TTS_AR_DBG")) P.dbg_flags = atoi(e);   // bring-up A/B switches (ar_params.h dbg_flags)
   if (cluster) {
     P.G = kDecCtas;
     P.y = h->d_y;
     P.mt_max = 1;
     P.n_slots = smem_max_slots(1, h->smem_budget);
-    if (const char* e = getenv("TTS_AR_DBG")) P.dbg_flags = atoi(e);
     if (const char* e = getenv("TTS_AR_SLOTS")) P.n_slots = std::max(2, std::min(P.n_slots, atoi(e)));   // bring-up: ring depth
     TTS_CUDA(h, cudaMemsetAsync(h->d_y, 0, sizeof(long long) * kDecRows * kD, st));
     e = launch_decode(P, smem_total_bytes(1, P.n_slots), st);
