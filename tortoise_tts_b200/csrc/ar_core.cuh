@@ -83,10 +83,13 @@ __device__ __forceinline__ bool gemm_desc(const Params& P, const Instr& ins, Gem
 struct ProgIter {
   int layer, op, group, rot, phase;   // phase 0: sample, 1: layers, 2: tail, 3: done
   int n_groups, n_head_groups;
+  int row_group;   // rows per GEMM instruction: 128 (8 m-tiles, one per warp) when the A operand comes from L2 (LayerNorm
+                   // phase active), else kRowGroup = 64 (the LayerNorm'd rows must fit the shared-memory A buffer)
   __device__ __forceinline__ void reset(const Params& P) {
     phase = P.has_sample ? 0 : 1;
     layer = 0; op = OP_LN_QKV; group = 0; rot = 0;
-    n_groups = (P.n_rows + kRowGroup - 1) / kRowGroup;
+    row_group = (P.xn != nullptr && P.n_rows > kLnSplitMinRows && !(P.dbg_flags & 8)) ? 2 * kRowGroup : kRowGroup;
+    n_groups = (P.n_rows + row_group - 1) / row_group;
     n_head_groups = (P.n_head_rows + kRowGroup - 1) / kRowGroup;
   }
   __device__ __forceinline__ bool next(const Params& P, Instr& in) {
@@ -103,8 +106,8 @@ struct ProgIter {
         op = OP_PROJ;
         return true;
       }
-      in.row0 = group * kRowGroup;
-      in.nrows = min(kRowGroup, P.n_rows - in.row0);
+      in.row0 = group * row_group;
+      in.nrows = min(row_group, P.n_rows - in.row0);
       in.flags = (group == 0) ? F_BARRIER_BEFORE : 0;
       if (group == 0 && op == OP_LN_QKV && layer == 0 && P.has_sample) in.flags |= F_CHECK_EXIT | F_PLAN;
       if (++group == n_groups) {

@@ -74,7 +74,7 @@ __device__ __forceinline__ void gemm_epilogue(const Params& P, const Instr& ins,
   }
 }
 
-// MT = M-tiles of 16 rows in this instruction (1, 2 or 4).  Warp w: m-tile w % MT, k-slice w / MT.
+// MT = M-tiles of 16 rows in this instruction (1, 2, 4 or 8; 8 only with the A operand in L2).  Warp w: m-tile w % MT, k-slice w / MT.
 // Tiles of this CTA: t0 + (i / tinner) * tstride + i % tinner, i < cnt (tinner >= cnt = the contiguous schedule
 // of tile_range).
 template <int MT>

@@ -73,7 +73,8 @@ __global__ void __launch_bounds__(kThreads, 1) ar_program_kernel(const __grid_co
           const int mt = (ins.nrows + 15) >> 4;
           if (mt <= 1) gemm_stage<1>(P, ins, sm, pipe);
           else if (mt == 2) gemm_stage<2>(P, ins, sm, pipe);
-          else gemm_stage<4>(P, ins, sm, pipe);
+          else if (mt <= 4) gemm_stage<4>(P, ins, sm, pipe);
+          else gemm_stage<8>(P, ins, sm, pipe);
           break;
         }
         case OP_ATTN:

@@ -34,7 +34,7 @@ struct Instr {
   int op;
   int layer;
   int row0;     // first row (multiple of 16)
-  int nrows;    // rows in this instruction (<= kRowGroup for GEMM ops; all rows for ATTN/SAMPLE/LATENT)
+  int nrows;    // rows in this instruction (<= 128 for GEMM ops, ProgIter::row_group; all rows for ATTN/SAMPLE/LATENT)
   int flags;
   int rot;      // tile-schedule rotation (layout.h tile_range)
   int pad0, pad1;
@@ -134,7 +134,7 @@ struct Params {
   int n_steps;
   unsigned long long* prof;   // nullable: CTA 0 stage timestamps (ns) of step prof_step: [2*pc] before / [2*pc+1] after the barrier
   int prof_step;
-  int dbg_flags;         // bring-up A/B switches (TTS_AR_DBG): bit 0 = per-CTA LayerNorm instead of the cluster-cooperative one; bit 1 = prompt-pass attention as one decode-shaped unit per (row, head) instead of 16-row mma tiles; bit 2 = 16-row tiles whatever the row count
+  int dbg_flags;         // bring-up A/B switches (TTS_AR_DBG): bit 0 = per-CTA LayerNorm instead of the cluster-cooperative one; bit 1 = prompt-pass attention as one decode-shaped unit per (row, head) instead of 16-row mma tiles; bit 2 = 16-row tiles whatever the row count; bit 3 = 64-row GEMM instructions even when the A operand comes from L2
   int skip_last_model;   // generate(): the model is not run after the last sampled token
 };
 

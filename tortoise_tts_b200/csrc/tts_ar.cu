@@ -64,7 +64,7 @@ static int create_impl(TtsArHandle* h) {
   const int rf_pages = rf_batch * ((rf_len + kPage - 1) / kPage);
   h->n_pages = std::max(c.max_utts * h->npp + c.max_seqs * h->nqp, rf_pages);
   h->rows_cap = std::max({c.max_seqs, c.max_utts * h->plen_max, h->rf_rows_cap});
-  h->rows_cap = (h->rows_cap + 63) / 64 * 64;
+  h->rows_cap = (h->rows_cap + 127) / 128 * 128;    // 128-row GEMM instructions read whole m-tiles
   h->logit_rows_cap = (std::max(c.max_seqs, c.max_utts) + 63) / 64 * 64;
   h->plan_cap_units = std::max(h->G * kNW, 1);
   h->seen_words = (c.n_mel_codes + 31) / 32;
