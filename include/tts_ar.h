@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define TTS_AR_ABI_VERSION 1
+#define TTS_AR_ABI_VERSION 2
 #define TTS_AR_MODEL_DIM 1024   /* compiled-in: d_model, 16 heads x 64 (unified_voice.py:336-338) */
 #define TTS_AR_HEADS 16
 #define TTS_AR_HEAD_DIM 64
@@ -165,11 +165,12 @@ int tts_ar_forward_latents(TtsArHandle* h, const float* latent, const int32_t* t
                            const int32_t* codes_len, int32_t n, float* out, void* stream);
 
 /* Whole inference_speech call on HOST buffers: H2D of latent/text, prefill, generate, D2H of the
- * codes, all on `stream`, then waits for it.  SYNC.  This is the end-to-end entry bench.py times. */
+ * codes, all on `stream` (the caller's, like every other entry point), then waits for it.  SYNC.
+ * This is the end-to-end entry bench.py times. */
 int tts_ar_inference_speech_host(TtsArHandle* h, const float* latent_host, const int32_t* text_host,
                                  int32_t text_stride, const int32_t* text_len, int32_t n_utt,
                                  int32_t n_cand, const TtsArSampling* s, int32_t max_new,
-                                 int64_t* out_codes_host, int32_t* steps_run);
+                                 int64_t* out_codes_host, int32_t* steps_run, void* stream);
 
 /* Epilogue between the sampler and its callers, in place on device codes [rows][stride] (int64):
  * reference tortoise_tts/inference.py:353-366 (and train.py:135-147): in a row that contains the stop token, it and
@@ -185,7 +186,23 @@ int tts_ar_fixup_codes(TtsArHandle* h, int64_t* codes, int32_t rows, int32_t len
  * [rows,1024]), "q", "logits", "cur_latent", "kv" (page pool, bf16), "ctx", "h" (bf16 fragment order). */
 int tts_ar_debug_copy(TtsArHandle* h, const char* name, void* dst, uint64_t bytes, void* stream);
 
-/* Waits for `stream`, then reports the last call's outcome. SYNC. */
+/* Parity hook for the tcgen05 / TMEM GEMM of the dense passes alone (csrc/tc_gemm.cuh):
+ * out[M][N] (dev fp32) = a[M][K] . wt[N][K]^T + bias[N]; a, wt dev bf16 row-major, K % 64 == 0, 16-byte aligned;
+ * bias nullable; bn = 128 or 256 selects the tile width.  ASYNC on `stream`. */
+int tts_ar_debug_gemm(TtsArHandle* h, const void* a_bf16, const void* wt_bf16, const float* bias, float* out,
+                      int32_t M, int32_t N, int32_t K, int32_t bn, void* stream);
+
+/* Explicit per-handle options (all default 0 unless noted); returns TTS_AR_ERR_BAD_ARG for unknown names/values.
+ *   "decode_kernel"      0 head-cluster kernels whenever their clusters are co-resident, 1 the interpreter kernel
+ *   "dense_kernel"       0 tcgen05 pipeline for the prompt pass / latent re-forward, 1 the interpreter kernel
+ *   "attn_tiles"         prompt-shaped attention: 0 auto, 1 one unit per (row, head), 2 always 16-row mma tiles
+ *   "cooperative_launch" 1 (default) cooperative cluster launch, 0 plain cluster launch (profilers)
+ *   "prof_step"          decode step whose per-stage timestamps are recorded (scripts/stage_prof.py); -1 off */
+int tts_ar_set_option(TtsArHandle* h, const char* name, int32_t value);
+
+/* Waits for `stream`, then reports the last call's outcome (TTS_AR_ERR_WATCHDOG after a device-side time-out,
+ * TTS_AR_ERR_BAD_ARG when a token id was outside its embedding table -- the reference's nn.Embedding raises).
+ * Either condition is reported once and cleared. SYNC. */
 int tts_ar_sync_result(TtsArHandle* h, TtsArStats* out, void* stream);
 
 #ifdef __cplusplus

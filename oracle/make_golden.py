@@ -23,13 +23,19 @@ def versions():
     return dict(torch=torch.__version__, transformers=transformers.__version__, numpy=np.__version__)
 
 
-def case_l2():
+def case_l2(bf16_weights=False):
     """2 layers at full width, sharpened attention, 2 utterances x 2 candidates, greedy with
-    repetition_penalty 2.0 (train.py:127), plus the latent re-forward on the generated codes."""
+    repetition_penalty 2.0 (train.py:127), plus the latent re-forward on the generated codes.
+    bf16_weights=True -> ref_l2_bf16w.npz: every weight rounded to a bf16-representable value first (the reference
+    still computes in fp32), so the reference and the bf16 CUDA path hold IDENTICAL weights and the north-star
+    tolerance (2e-2) applies undiluted; ref_l2.npz keeps the unrounded fp32 weights (the bf16 snapshot of the
+    weights is then part of the error)."""
     cfg = ARConfig(layers=2)
     spec = dict(layers=2, w_seed=3, attn_std=0.08, in_seed=5, n_utt=2, text_len=12, n_cand=2,
-                max_new=10, repetition_penalty=2.0)
+                max_new=10, repetition_penalty=2.0, bf16_weights=bf16_weights)
     sd = make_state_dict(cfg, seed=spec["w_seed"], attn_std=spec["attn_std"])
+    if bf16_weights:
+        sd = {k: v.bfloat16().float() for k, v in sd.items()}
     lat, texts = make_inputs(cfg, spec["n_utt"], [spec["text_len"]] * spec["n_utt"], seed=spec["in_seed"])
     text = torch.stack(texts)
     m = ref_shim.build_reference_model(sd, cfg)
@@ -40,7 +46,7 @@ def case_l2():
     with torch.inference_mode():
         rl = m(l2, t2, torch.full((B,), t2.shape[1]), codes.clone(),
                torch.full((B,), codes.shape[1] * 1024), return_latent=True, clip_inputs=False)
-    np.savez_compressed(os.path.join(OUT, "ref_l2.npz"), spec=str(spec), versions=str(versions()),
+    np.savez_compressed(os.path.join(OUT, "ref_l2_bf16w.npz" if bf16_weights else "ref_l2.npz"), spec=str(spec), versions=str(versions()),
                         codes=r["codes"].numpy(), logits=r["logits"].numpy(),
                         latents=r["latents"].numpy(), pos_trace=np.array(r["pos_trace"]),
                         prefix_len=r["prefix_len"], reforward_codes=codes.numpy(),
@@ -102,5 +108,6 @@ if __name__ == "__main__":
     torch.set_num_threads(os.cpu_count())
     case_warpers()
     case_l2()
+    case_l2(bf16_weights=True)
     case_full()
     case_full(bf16_weights=True)

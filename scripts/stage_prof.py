@@ -20,6 +20,8 @@ sd = make_state_dict(cfg, seed=0)
 lat, texts = make_inputs(cfg, 1, [64], seed=1)
 text = torch.stack(texts)
 m = UnifiedVoiceB200(sd, ARGeometry(layers=layers), max_utts=1, max_seqs=n_cand, max_text_len=64, max_new_tokens=520)
+if "TTS_AR_PROF_STEP" in os.environ:
+    m.set_option("prof_step", int(os.environ["TTS_AR_PROF_STEP"]))
 kw = dict(do_sample=True, top_p=0.8, temperature=0.8, top_k=0, seed=1234, ignore_eos=True)
 for _ in range(2):
     m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=n_cand, max_generate_length=steps, **kw)

@@ -21,7 +21,28 @@ from oracle.weights import ARConfig, make_inputs, make_state_dict
 pytestmark = pytest.mark.gpu
 
 BF16_REL = 2e-2          # north_star: "prefill and step logits within 2e-2 relative error in bf16"
-STRESS_REL = 4e-2        # sharpened-attention stress weights (attn_std 0.08): torch's own bf16 path is at 2.4e-2
+STRESS_REL = 4e-2        # ref_l2.npz only: the reference holds UNROUNDED fp32 weights there, so the bf16 snapshot of sharpened (attn_std 0.08)
+                         # weights is part of the error; ref_l2_bf16w.npz (identical weights) is held to BF16_REL
+
+
+PARITY = {}              # measured errors / agreements of this run -> parity_r02.json (gpurun_out/ on the GPU box)
+
+
+def record(name, **kw):
+    PARITY.setdefault(name, {}).update({k: (float(v) if isinstance(v, (int, float, np.floating)) else v) for k, v in kw.items()})
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _write_parity_record():
+    yield
+    import json
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out_dir = os.path.join(root, "gpurun_out") if os.path.isdir(os.path.join(root, "gpurun_out")) else os.path.join(root, "profiles")
+    try:
+        with open(os.path.join(out_dir, "parity_r02.json"), "w") as f:
+            json.dump({"bars": {"bf16_rel": BF16_REL, "greedy_identical": 0.99}, "measured": PARITY}, f, indent=1, sort_keys=True)
+    except OSError:
+        pass
 
 
 def rel(a, b):
@@ -42,14 +63,18 @@ def bf16_weights(sd):
     return {k: v.bfloat16().float() for k, v in sd.items()}
 
 
-@pytest.fixture(scope="module")
-def l2_case(golden_dir):
-    g = np.load(os.path.join(golden_dir, "ref_l2.npz"))
+@pytest.fixture(scope="module", params=["ref_l2_bf16w.npz", "ref_l2.npz"])
+def l2_case(golden_dir, request):
+    g = np.load(os.path.join(golden_dir, request.param))
     spec = ast.literal_eval(str(g["spec"]))
     cfg = ARConfig(layers=spec["layers"])
     sd = make_state_dict(cfg, seed=spec["w_seed"], attn_std=spec["attn_std"])
+    tol = STRESS_REL
+    if spec.get("bf16_weights"):
+        sd = bf16_weights(sd)
+        tol = BF16_REL
     lat, texts = make_inputs(cfg, spec["n_utt"], [spec["text_len"]] * spec["n_utt"], seed=spec["in_seed"])
-    return g, spec, cfg, sd, lat, torch.stack(texts)
+    return g, spec, cfg, sd, lat, torch.stack(texts), tol, request.param
 
 
 # ---- against the reference's golden vectors ------------------------------------------------------------
@@ -57,15 +82,17 @@ def test_l2_reference_golden_teacher_forced(b200, l2_case):
     """2 layers, sharpened attention, 2 utterances x 2 candidates, repetition_penalty 2.0: prefill and
     step logits, per-step latents, greedy choices under teacher forcing with the reference's codes."""
     UV, Geo = b200
-    g, spec, cfg, sd, lat, text = l2_case
+    g, spec, cfg, sd, lat, text, tol, gname = l2_case
     m = UV(sd, Geo(layers=2), max_utts=2, max_seqs=4, max_text_len=16, max_new_tokens=16)
     ref_codes = torch.from_numpy(g["codes"])
     codes, lats, choice = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=2, max_generate_length=10,
                                              repetition_penalty=2.0, forced_tokens=ref_codes, return_latents=True,
                                              return_choice=True)
     assert torch.equal(codes.cpu(), ref_codes)                       # forced ids are written back bit-exact
-    assert rel(lats, g["latents"]) < STRESS_REL
+    e_lat = rel(lats, g["latents"])
     agree = (choice.cpu().long() == ref_codes).float().mean().item()
+    record("l2_golden_teacher_forced/" + gname, latents_rel=e_lat, choice_agreement=agree, tol=tol)
+    assert e_lat < tol, e_lat
     assert agree >= 0.9, agree
     # step logits through the streaming entry (tts_ar_step), still teacher-forced
     m._prefill(lat.cuda(), text.cuda(), 2)
@@ -78,14 +105,15 @@ def test_l2_reference_golden_teacher_forced(b200, l2_case):
                                    C.c_void_p(forced.data_ptr()), C.c_void_p(0), m._stream()), "step")
         m.sync_stats()
         errs.append(rel(m.logits_debug(), g["logits"][k + 1]))
-    assert max(errs) < STRESS_REL, errs
+    record("l2_golden_teacher_forced/" + gname, step_logits_rel=max(errs))
+    assert max(errs) < tol, errs
     m.close()
 
 
 def test_l2_reference_golden_latent_reforward(b200, l2_case):
     """UnifiedVoice.forward(return_latent=True) (unified_voice.py:544-600) vs the reference's output."""
     UV, Geo = b200
-    g, spec, cfg, sd, lat, text = l2_case
+    g, spec, cfg, sd, lat, text, tol, gname = l2_case
     m = UV(sd, Geo(layers=2), max_utts=2, max_seqs=4, max_text_len=16, max_new_tokens=16)
     codes = torch.from_numpy(g["reforward_codes"])
     B, M = codes.shape
@@ -93,7 +121,13 @@ def test_l2_reference_golden_latent_reforward(b200, l2_case):
     out = m.forward(l2.cuda(), t2.cuda(), torch.full((B,), t2.shape[1]), codes.cuda(), torch.full((B,), M * 1024),
                     return_latent=True, clip_inputs=False)
     assert out.shape == (B, M, 1024)
-    assert rel(out, g["reforward_latents"]) < STRESS_REL
+    e = rel(out, g["reforward_latents"])
+    record("l2_golden_latent_reforward/" + gname, latents_rel=e, tol=tol)
+    assert e < tol, e
+    # the reference caller's own shapes: lengths as [n, 1] (inference.py:371-379 wav_lengths.repeat(candidates, 1))
+    out2 = m.forward(l2.cuda(), t2.cuda(), torch.full((B, 1), t2.shape[1]), codes.cuda(), torch.full((B, 1), M * 1024),
+                     return_latent=True, clip_inputs=False)
+    assert torch.equal(out2, out)
     m.close()
 
 
@@ -129,9 +163,12 @@ def test_full_c1_reference_golden(full_model, golden_dir):
     clear = gap > 2 * e0 * scale                      # the reference's own decision is outside our error band
     print(f"C1 teacher-forced agreement {same.mean():.4f} overall, {same[clear].mean():.4f} on {clear.sum()} clear steps; "
           f"prefill logits rel err {e0:.2e}")
+    e_lat = rel(lats[:, [0, 1, 199]], g["latents_sel"])
+    record("c1_full_golden", prefill_logits_rel=e0, greedy_identical=float(same.mean()), greedy_identical_clear=float(same[clear].mean()),
+           latents_rel=e_lat)
     assert same[clear].mean() >= 0.99
-    assert same.mean() >= 0.95
-    assert rel(lats[:, [0, 1, 199]], g["latents_sel"]) < BF16_REL
+    assert same.mean() >= 0.99             # north star: greedy-decode token sequences at least 99% identical
+    assert e_lat < BF16_REL
 
 
 def test_full_c1_original_fp32_weights(b200, golden_dir):
@@ -264,7 +301,8 @@ def test_greedy_free_running_matches_oracle(b200):
             assert gap < BF16_REL, (r, k, gap)
             assert int(got[r, k]) in torch.topk(sc, 2).indices.tolist()
     print("free-running greedy: identical prefix fraction", n_same / (4 * steps))
-    assert n_same / (4 * steps) >= 0.5
+    record("greedy_free_running_l2", identical_prefix_fraction=n_same / (4 * steps))
+    assert n_same / (4 * steps) >= 0.5     # every divergence is asserted above to sit at a reference near-tie
     m.close()
 
 
@@ -346,7 +384,7 @@ def test_sampling_is_invariant_to_sharding(b200):
     m.close()
 
 
-def test_head_cluster_kernel_agrees_with_interpreter_kernel(b200, monkeypatch):
+def test_head_cluster_kernel_agrees_with_interpreter_kernel(b200):
     """<= 16 sequences decode in ar_decode_kernel (32 clusters of 4 CTAs); more, or TTS_AR_DECODE=interp, in the
     interpreter kernel.  Same weights, same teacher-forced tokens: per-step latents agree to bf16-path noise, the
     sampler picks are the same wherever the oracle margin is not a near-tie, and the pad/stop bookkeeping is identical.
@@ -354,11 +392,8 @@ def test_head_cluster_kernel_agrees_with_interpreter_kernel(b200, monkeypatch):
     kw = dict(do_sample=True, top_p=0.8, temperature=0.8, top_k=0, seed=11, max_generate_length=14, ignore_eos=True)
     outs = {}
     for mode in ("cluster", "interp"):
-        if mode == "interp":
-            monkeypatch.setenv("TTS_AR_DECODE", "interp")
-        else:
-            monkeypatch.delenv("TTS_AR_DECODE", raising=False)
         m, o, cfg, lat, texts = make_small(b200, U=1, T=12, max_utts=1, max_seqs=7, max_new_tokens=16)
+        m.set_option("decode_kernel", 1 if mode == "interp" else 0)
         text = torch.stack(texts)
         free = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=7, **kw).cpu()
         forced = outs["cluster"][0] if mode == "interp" else free
@@ -609,7 +644,7 @@ def test_32_sequences_run_as_two_head_cluster_groups_bit_exact(b200):
     m.close()
 
 
-def test_dense_pass_tiled_attention_matches_oracle_and_row_path(b200, monkeypatch):
+def test_dense_pass_tiled_attention_matches_oracle_and_row_path(b200):
     """Prompt-shaped passes with >= 1184 rows run their causal attention as 16-row mma tiles (csrc/ar_attn.cuh
     attn_tile16; below that one decode-shaped unit per (row, head)).  The latent re-forward (unified_voice.py:544-600)
     of 4 sequences x 317 positions crosses the threshold: vs the fp32 oracle at the bf16 tolerance, and vs the row path
@@ -627,14 +662,194 @@ def test_dense_pass_tiled_attention_matches_oracle_and_row_path(b200, monkeypatc
     want = o.forward_latents(lat, text, codes)
     m = UV(sd, Geo(layers=2), max_utts=4, max_seqs=4, max_text_len=16, max_new_tokens=M + 4)
     args = (lat.cuda(), text.cuda(), torch.full((4,), 12), codes.cuda(), torch.full((4,), M * 1024))
-    monkeypatch.delenv("TTS_AR_DBG", raising=False)
+    m.set_option("attn_tiles", 2)
     tiled = m.forward(*args, return_latent=True, clip_inputs=False).cpu()
-    monkeypatch.setenv("TTS_AR_DBG", "2")
+    m.set_option("attn_tiles", 1)
     rows = m.forward(*args, return_latent=True, clip_inputs=False).cpu()
-    monkeypatch.delenv("TTS_AR_DBG")
+    m.set_option("attn_tiles", 0)
+    m.set_option("dense_kernel", 1)          # the interpreter kernel in prompt mode (fallback path) agrees with the tcgen05 pipeline
+    interp = m.forward(*args, return_latent=True, clip_inputs=False).cpu()
+    m.set_option("dense_kernel", 0)
+    e_i = rel(interp, want)
+    record("dense_pass_4x317", tiled_vs_oracle=rel(tiled, want), rows_vs_oracle=rel(rows, want), interpreter_vs_oracle=e_i)
+    assert e_i < BF16_REL
     assert tiled.shape == (4, M, 1024)
     e_t, e_r, e_tr = rel(tiled, want), rel(rows, want), rel(tiled, rows)
     print(f"dense attention: tiled vs oracle {e_t:.3e}, row path vs oracle {e_r:.3e}, tiled vs row path {e_tr:.3e}")
     assert e_t < BF16_REL and e_r < BF16_REL and e_tr < BF16_REL
     assert not torch.equal(tiled, rows)          # the two paths really are different code
     m.close()
+
+
+# ---- the tcgen05 / TMEM GEMM of the dense passes, alone ------------------------------------------------------------------
+@pytest.mark.parametrize("M,N,K,bn", [(128, 128, 64, 128), (300, 384, 1024, 128), (1000, 3072, 1024, 256),
+                                      (257, 8194, 1024, 128), (130, 1024, 4096, 256), (68, 4096, 1024, 128)])
+def test_tc_gemm_matches_torch(b200, M, N, K, bn):
+    """csrc/tc_gemm.cuh (tcgen05.mma, TMA-staged 128-byte-swizzled operands, TMEM accumulators) through the C-ABI parity
+    hook: out = A . Wt^T + bias with bf16 operands and fp32 accumulation vs torch fp32 on the same bf16 values.  Covers
+    ragged M (TMA zero fill, masked rows), ragged N (mel head: 8194 columns), both tile widths, K = 64 .. 4096."""
+    m, o, cfg, lat, texts = make_small(b200, U=1, T=8, max_utts=1, max_seqs=2, max_new_tokens=8)
+    g = torch.Generator().manual_seed(M * 7 + N)
+    a = torch.randn(M, K, generator=g).bfloat16().cuda()
+    wt = (torch.randn(N, K, generator=g) * 0.05).bfloat16().cuda()
+    bias = torch.randn(N, generator=g).cuda()
+    out = torch.full((M, N), float("nan"), device="cuda")
+    m._check(m.lib.tts_ar_debug_gemm(m.handle, C.c_void_p(a.data_ptr()), C.c_void_p(wt.data_ptr()), C.c_void_p(bias.data_ptr()),
+                                     C.c_void_p(out.data_ptr()), M, N, K, bn, m._stream()), "tts_ar_debug_gemm")
+    m.sync_stats()
+    want = a.float() @ wt.float().t() + bias
+    e = rel(out, want)
+    record(f"tc_gemm/{M}x{N}x{K}/bn{bn}", rel=e)
+    assert torch.isfinite(out).all()
+    assert e < 1e-4, e                       # fp32 accumulation of exact bf16 products: summation-order noise only
+    m.close()
+
+
+# ---- BASELINE shapes against the oracle (VERDICT round 1, item 1) ------------------------------------------------------
+def test_c2_full_size_teacher_forced_vs_oracle(full_model):
+    """BASELINE config C2 at FULL size (30 layers, 16 candidates of one 64-token utterance), teacher-forced for 8 steps
+    with a fixed token matrix: per-step latents and step logits within 2e-2 of the fp32 oracle on identical
+    (bf16-representable) weights, the sampler's greedy choice equal to the oracle's wherever the oracle's top-2 gap is
+    outside the measured error band."""
+    m, cfg, lat, text = full_model
+    steps, N = 8, 16
+    forced = torch.randint(0, 8192, (N, steps), generator=torch.Generator().manual_seed(21))
+    sd = bf16_weights(make_state_dict(cfg, seed=0))
+    o = OracleAR(sd, cfg)
+    torch.set_num_threads(os.cpu_count() or 1)
+    with torch.inference_mode():
+        ref = o.generate(lat, text, n_cand=N, max_new=steps, forced=forced, want_logits=steps, ignore_eos=True)
+    codes, lats, choice = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=N, max_generate_length=steps,
+                                             forced_tokens=forced, return_latents=True, return_choice=True, ignore_eos=True)
+    assert torch.equal(codes.cpu(), forced)
+    e_lat = rel(lats, ref["latents"])
+    # step logits of the last step through the parity hook (state after `steps - 1` fed tokens)
+    m._prefill(lat.cuda(), text.cuda(), N)
+    s = m._sampling(dict(do_sample=False, ignore_eos=True))
+    errs = [rel(m.logits_debug(), ref["logits"][0][:1])]
+    for k in range(3):
+        out = torch.zeros(N, 1, dtype=torch.int64, device="cuda")
+        f = forced[:, k:k + 1].to("cuda", torch.int32).contiguous()
+        m._check(m.lib.tts_ar_step(m.handle, C.byref(s), 1, C.c_void_p(out.data_ptr()), C.c_void_p(0), C.c_void_p(f.data_ptr()),
+                                   C.c_void_p(0), m._stream()), "step")
+        m.sync_stats()
+        errs.append(rel(m.logits_debug(), ref["logits"][k + 1]))
+    e_log = max(errs)
+    scale = ref["logits"].abs().amax(dim=(1, 2))                       # per step
+    top2 = torch.topk(ref["logits"], 2, dim=-1).values
+    gap = (top2[..., 0] - top2[..., 1]) / scale[:, None]               # [steps, N]
+    clear = (gap > 2 * e_log).t()
+    same = choice.cpu().long() == ref["choice"]
+    record("c2_full_size_teacher_forced", latents_rel=e_lat, step_logits_rel=e_log, choice_agreement=float(same.float().mean()),
+           choice_agreement_clear=float(same[clear].float().mean()), clear_fraction=float(clear.float().mean()))
+    print(f"C2 full size: latents {e_lat:.2e}, step logits {e_log:.2e}, choices {same.float().mean():.3f} ({same[clear].float().mean():.3f} clear)")
+    assert e_lat < BF16_REL and e_log < BF16_REL
+    assert bool(same[clear].all())
+
+
+@pytest.mark.parametrize("U,N", [(3, 16), (4, 16), (8, 16), (1, 24), (1, 32), (2, 16)])
+def test_many_sequences_ragged_vs_oracle(b200, U, N):
+    """More than 16 sequences (the shapes the C3 / C4 / C5 per-GPU shares run: 24, 32, 48, 64, 128), ragged text lengths,
+    44 teacher-forced steps so private KV pages cross a page boundary and long rows are split over several attention
+    units; rows finish at different steps (forced stop tokens).  Quirk Q8 contract: per utterance, the latents equal the
+    oracle's run on that utterance ALONE (<= 2e-2), codes / padding / termination bit-exact."""
+    steps = 44
+    rng = np.random.default_rng(U * 100 + N)
+    lens = [int(x) for x in rng.integers(5, 41, size=U)]
+    B = U * N
+    m, o, cfg, lat, texts = make_small(b200, U=U, T=lens, max_utts=U, max_seqs=B, max_new_tokens=48)
+    Tm = max(lens)
+    text = torch.zeros(U, Tm, dtype=torch.long)
+    for u, t in enumerate(texts):
+        text[u, : len(t)] = t
+    forced = torch.from_numpy(rng.integers(0, 8192, size=(B, steps))).long()
+    stop = cfg.stop_mel_token
+    stops = {}
+    for r in range(0, B, 3):                                         # every third row stops somewhere in [4, steps)
+        k = int(rng.integers(4, steps))
+        forced[r, k] = stop
+        stops[r] = k
+    got, lats = m.inference_speech(lat.cuda(), text.cuda(), num_return_sequences=N, max_generate_length=steps,
+                                   text_lengths=lens, forced_tokens=forced, return_latents=True)
+    got, lats = got.cpu(), lats.cpu()
+    worst = 0.0
+    for u in range(U):
+        ref = o.generate(lat[u:u + 1], texts[u][None], n_cand=N, max_new=steps, forced=forced[N * u: N * u + N])
+        n = ref["codes"].shape[1]                                    # the oracle stops when ITS rows have all finished (never: some run on)
+        assert torch.equal(got[N * u: N * u + N, :n], ref["codes"]), u
+        for r in range(N):
+            k = stops.get(N * u + r, steps)
+            valid = min(k + 1, n)                                    # latents of steps up to and including the stop step are defined
+            e = rel(lats[N * u + r, :valid], ref["latents"][r, :valid])
+            worst = max(worst, e)
+    for r, k in stops.items():
+        assert (got[r, k:] == stop).all()                            # pad after stop (Q7)
+    record(f"ragged_vs_oracle/U{U}xN{N}", latents_rel=worst, sequences=B, steps=steps)
+    print(f"U={U} N={N}: worst per-row latents rel err {worst:.2e}")
+    assert worst < BF16_REL
+    m.close()
+
+
+# ---- the drop-in boundary: patch_reference_module on a reference-shaped module ----------------------------------------
+def test_patch_reference_module_with_reference_call_sites(b200):
+    """`patch_reference_module` on a module with the reference's attribute names / state_dict keys (tests/standin.py),
+    called with exactly the kwargs of the reference's callers: inference.py:334-346 (inference_speech), :266-285
+    (compute_embeddings + get_generator), :371-379 (forward(return_latent=True) with repeated [n, 1] lengths) and
+    train.py:119-129; results equal a UnifiedVoiceB200 built directly from the same weights.  A LoRA parametrization
+    (reference lora.py:163-195) on c_attn must change the result exactly as merged weights do."""
+    import torch.nn.utils.parametrize as parametrize
+    from tests.standin import LoRADelta, StandInUnifiedVoice
+    from tortoise_tts_b200 import patch_reference_module
+    UV, Geo = b200
+    cfg = ARConfig(layers=2)
+    sd = bf16_weights(make_state_dict(cfg, seed=7, attn_std=0.04))
+    lat, texts = make_inputs(cfg, 1, [12], seed=9)
+    text = torch.stack(texts)
+    mod = StandInUnifiedVoice(cfg, sd).cuda()
+    patch_reference_module(mod, max_utts=1, max_seqs=4, max_text_len=16, max_new_tokens=40)
+    direct = UV(sd, Geo(layers=2), max_utts=1, max_seqs=4, max_text_len=16, max_new_tokens=40)
+    candidates = 2
+    kw = dict(do_sample=True, top_k=50, top_p=0.8, temperature=0.8, num_return_sequences=candidates, num_beams=1,
+              length_penalty=1.0, repetition_penalty=2.0, max_generate_length=24)
+    codes = mod.inference_speech(lat.cuda(), text.cuda(), **kw)                                   # inference.py:334-346
+    want = direct.inference_speech(lat.cuda(), text.cuda(), **kw)
+    assert codes.dtype == torch.int64 and codes.is_cuda and torch.equal(codes, want)
+    codes[0, -1] = 83                                                                             # the caller mutates the result in place (inference.py:360-366)
+    # forward(return_latent=True) with the caller's repeated [n, 1] lengths                       # inference.py:371-379
+    text_lengths = torch.Tensor([text.shape[1]]).to(dtype=torch.int32)
+    wav_lengths = torch.tensor([codes.shape[-1] * mod.mel_length_compression], device="cuda")
+    l1 = mod.forward(lat.cuda().repeat(candidates, 1), text.cuda().repeat(candidates, 1), text_lengths.repeat(candidates, 1), codes,
+                     wav_lengths.repeat(candidates, 1), return_latent=True, clip_inputs=False)
+    l2 = direct.forward(lat.cuda().repeat(candidates, 1), text.cuda().repeat(candidates, 1), torch.full((candidates,), text.shape[1]),
+                        codes, torch.full((candidates,), codes.shape[-1] * 1024), return_latent=True, clip_inputs=False)
+    assert l1.shape == (candidates, codes.shape[1], 1024) and torch.equal(l1, l2)
+    assert mod.forward(1, 2) == "reference forward"                                               # every other forward() stays the reference's
+    # streaming call site                                                                         # inference.py:266-285
+    inputs = mod.compute_embeddings(lat.cuda(), text.cuda())
+    gen = mod.get_generator(inputs=inputs, top_k=50, top_p=0.8, temperature=0.8, do_sample=True, num_beams=1, num_return_sequences=1,
+                            length_penalty=1.0, repetition_penalty=2.0, output_attentions=False, output_hidden_states=True)
+    toks = []
+    for c, latent in gen:
+        assert c.shape == (1,) and latent.shape == (1, 1024)
+        toks.append(int(c[0]))
+        if len(toks) == 12:
+            break
+    one = direct.inference_speech(lat.cuda(), text.cuda(), do_sample=True, top_k=50, top_p=0.8, temperature=0.8, repetition_penalty=2.0,
+                                  max_generate_length=12)
+    assert toks == one[0, : len(toks)].tolist()
+    # LoRA: parametrized c_attn of layer 1 -> re-patch -> equals a model built from the merged weights
+    layer = mod.gpt.h[1].attn.c_attn
+    parametrize.register_parametrization(layer, "weight", LoRADelta(tuple(layer.weight.shape), seed=3).cuda())
+    mod._b200.load_state_dict(UV.module_weights(mod))                                             # "refresh after LoRA toggles" (lora.py:197-205)
+    sd2 = dict(sd)
+    lo = layer.parametrizations.weight[0]
+    sd2["gpt.h.1.attn.c_attn.weight"] = sd["gpt.h.1.attn.c_attn.weight"] + ((lo.lora_B @ lo.lora_A).detach() * lo.scaling).cpu()
+    merged = UV(sd2, Geo(layers=2), max_utts=1, max_seqs=4, max_text_len=16, max_new_tokens=40)
+    kw2 = dict(do_sample=False, num_return_sequences=1, repetition_penalty=2.0, max_generate_length=16)   # train.py:119-129 (greedy eval)
+    a = mod.inference_speech(lat.cuda(), text.cuda(), **kw2)
+    b = merged.inference_speech(lat.cuda(), text.cuda(), **kw2)
+    c = direct.inference_speech(lat.cuda(), text.cuda(), **kw2)
+    assert torch.equal(a, b)
+    assert not torch.equal(a, c)                      # the delta is really in: the base model decodes something else
+    for x in (mod._b200, direct, merged):
+        x.close()

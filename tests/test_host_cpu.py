@@ -29,7 +29,7 @@ def test_c_abi_exports_every_declared_symbol(built):
     for name in declared:
         assert hasattr(lib, name), name
     lib.tts_ar_abi_version.restype = C.c_int
-    assert lib.tts_ar_abi_version() == 1
+    assert lib.tts_ar_abi_version() == 2
     from tortoise_tts_b200 import _lib
     assert set(_lib.SYMBOLS) == declared
 
@@ -301,3 +301,62 @@ def test_threshold_search_keeps_the_typical_support_set(std, mass):
             near_mass = min(abs(cum[j] - mass), abs((cum[j - 1] if j else 0.0) - mass)) < 1e-5
             assert len(diff) <= 2 and (near_mass or np.all(np.abs(sh[diff] - thr) < 1e-5 * max(1.0, thr))), (diff[:5], sh[diff][:5], thr)
         assert mine.sum() >= 1 and rounds <= 16, rounds
+
+
+def test_module_weights_reads_lora_merged_values():
+    """Boundary: `from_module` collects weights by reading `.weight` (the LoRA-merged value under
+    torch.nn.utils.parametrize, reference lora.py:163-195), not `state_dict()` (which holds
+    `parametrizations.weight.original`, the un-merged base)."""
+    import torch
+    import torch.nn.utils.parametrize as parametrize
+    from tests.standin import LoRADelta, StandInUnifiedVoice
+    from tortoise_tts_b200.synthetic import ARConfig, make_state_dict
+    from tortoise_tts_b200.unified_voice import UnifiedVoiceB200
+    cfg = ARConfig(layers=2, model_dim=64, heads=2, number_mel_codes=40, start_mel_token=38, stop_mel_token=39,
+                   max_text_tokens=10, max_mel_tokens=12, number_text_tokens=15, start_text_token=15)
+    sd = make_state_dict(cfg, seed=1)
+    mod = StandInUnifiedVoice(cfg, sd)
+    plain = UnifiedVoiceB200.module_weights(mod)
+    assert set(sd) <= set(plain)
+    for k, v in sd.items():
+        assert torch.equal(plain[k], v), k
+    layer = mod.gpt.h[1].attn.c_attn
+    parametrize.register_parametrization(layer, "weight", LoRADelta(tuple(layer.weight.shape), seed=3))
+    assert "gpt.h.1.attn.c_attn.weight" not in mod.state_dict()                    # what state_dict() would have missed
+    assert "gpt.h.1.attn.c_attn.parametrizations.weight.original" in mod.state_dict()
+    merged = UnifiedVoiceB200.module_weights(mod)
+    lo = layer.parametrizations.weight[0]
+    want = sd["gpt.h.1.attn.c_attn.weight"] + (lo.lora_B @ lo.lora_A).detach() * lo.scaling
+    assert torch.allclose(merged["gpt.h.1.attn.c_attn.weight"], want)
+    assert not torch.equal(merged["gpt.h.1.attn.c_attn.weight"], sd["gpt.h.1.attn.c_attn.weight"])
+    assert torch.equal(merged["gpt.h.0.attn.c_attn.weight"], sd["gpt.h.0.attn.c_attn.weight"])
+    lo.enabled = False                                                             # disable_lora (lora.py:204-205)
+    assert torch.equal(UnifiedVoiceB200.module_weights(mod)["gpt.h.1.attn.c_attn.weight"], sd["gpt.h.1.attn.c_attn.weight"])
+    # a swapped-in LoRALinear-style module (lora.py:21-92): base .weight + un-merged lora_A / lora_B
+    head = mod.mel_head
+    g = torch.Generator().manual_seed(9)
+    head.lora_B = torch.nn.Parameter(torch.randn(head.out_features, 4, generator=g) * 0.05)
+    head.lora_A = torch.nn.Parameter(torch.randn(4, head.in_features, generator=g) * 0.05)
+    head.scaling, head.merged, head.enabled = 0.5, False, True
+    w = UnifiedVoiceB200.module_weights(mod)["mel_head.weight"]
+    assert torch.allclose(w, sd["mel_head.weight"] + (head.lora_B @ head.lora_A).detach() * 0.5)
+    head.merged = True                                                             # eval() with merge_weights: already in .weight
+    assert torch.equal(UnifiedVoiceB200.module_weights(mod)["mel_head.weight"], sd["mel_head.weight"])
+
+
+def test_set_mel_padding_per_row_lengths():
+    """forward(): lengths arrive as [n] or [n, 1] (reference inference.py:371-379) and are applied per row like the
+    reference's set_mel_padding (unified_voice.py:494-506) -- host-side shape logic only."""
+    import torch
+    n, M, stop = 3, 6, 99
+    codes = torch.arange(n * M).reshape(n, M)
+    for wav in (torch.tensor([2048, 4096, 1024]), torch.tensor([[2048], [4096], [1024]])):
+        w = torch.as_tensor(wav).reshape(-1)
+        mel_lengths = torch.div(w, 1024, rounding_mode="trunc")
+        idx = torch.arange(M)[None, :]
+        out = torch.where(idx >= (mel_lengths[:, None] + 1), torch.full_like(codes, stop), codes)
+        ref = codes.clone()
+        for b in range(n):                         # the reference's loop
+            actual_end = int(mel_lengths[b]) + 1
+            ref[b, actual_end:] = stop
+        assert out.shape == (n, M) and torch.equal(out, ref)

@@ -13,8 +13,10 @@ SYMBOLS = [
     "tts_ar_abi_version", "tts_ar_create", "tts_ar_destroy", "tts_ar_last_error", "tts_ar_load_weights",
     "tts_ar_prefill", "tts_ar_generate", "tts_ar_step", "tts_ar_logits_debug", "tts_ar_forward_latents",
     "tts_ar_inference_speech_host", "tts_ar_sync_result", "tts_ar_debug_copy", "tts_ar_fixup_codes",
+    "tts_ar_debug_gemm", "tts_ar_set_option",
 ]
 
+ABI_VERSION = 2
 STATUS = {0: "OK", -1: "BAD_ARG", -2: "CAPACITY", -3: "CUDA", -4: "STATE", -5: "DEVICE", -6: "WATCHDOG"}
 
 
@@ -79,7 +81,9 @@ def load():
     lib.tts_ar_forward_latents.argtypes = [vp, f32p, i32p, i32, C.POINTER(C.c_int32), i32p, i32,
                                            C.POINTER(C.c_int32), i32, f32p, vp]
     lib.tts_ar_inference_speech_host.argtypes = [vp, f32p, i32p, i32, C.POINTER(C.c_int32), i32, i32,
-                                                 C.POINTER(TtsArSampling), i32, i64p, C.POINTER(C.c_int32)]
+                                                 C.POINTER(TtsArSampling), i32, i64p, C.POINTER(C.c_int32), vp]
+    lib.tts_ar_debug_gemm.argtypes = [vp, vp, vp, f32p, f32p, i32, i32, i32, i32, vp]
+    lib.tts_ar_set_option.argtypes = [vp, C.c_char_p, i32]
     lib.tts_ar_sync_result.argtypes = [vp, C.POINTER(TtsArStats), vp]
     lib.tts_ar_debug_copy.argtypes = [vp, C.c_char_p, vp, C.c_uint64, vp]
     lib.tts_ar_fixup_codes.argtypes = [vp, i64p, i32, i32, i32, i32, i32p, i32p, vp]
@@ -87,7 +91,7 @@ def load():
         getattr(lib, s)
         if s not in ("tts_ar_destroy", "tts_ar_last_error"):
             getattr(lib, s).restype = C.c_int
-    assert lib.tts_ar_abi_version() == 1
+    assert lib.tts_ar_abi_version() == ABI_VERSION
     _lib = lib
     return lib
 

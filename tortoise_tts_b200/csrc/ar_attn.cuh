@@ -14,7 +14,8 @@ namespace tts {
 constexpr float kLog2e = 1.4426950408889634f;
 
 __device__ __forceinline__ void write_ctx_pair(const Params& P, int row, int col, float v0, float v1) {
-  *reinterpret_cast<uint32_t*>(P.ctx + afrag_elem_offset(row, col, kD)) = pack_bf16x2(v0, v1);
+  const int64_t off = P.ctx_row_major ? (int64_t)row * kD + col : afrag_elem_offset(row, col, kD);
+  *reinterpret_cast<uint32_t*>(P.ctx + off) = pack_bf16x2(v0, v1);
 }
 
 // Builds the decode split plan for rows [0, nrows): executed by ONE warp.
@@ -323,7 +324,7 @@ static __device__ void attn_stage(const Params& P, const Instr& ins, const Smem&
   // is latency-bound: one decode-shaped unit per (row, head) spreads it over 16 x more warps and is faster, 8.8 vs 10.0 ms
   // at 540 rows); tiles that straddle two sequences fall back to one unit per row
   const int n_tiles = (nrows + 15) >> 4;
-  if (mode == 0 && P.decode_mode == 0 && !(P.dbg_flags & 2) && (n_tiles * kH >= P.G * kNW || (P.dbg_flags & 4))) {
+  if (mode == 0 && P.decode_mode == 0 && P.attn_tiles_mode != 1 && (n_tiles * kH >= P.G * kNW || P.attn_tiles_mode == 2)) {
     for (int ut = blockIdx.x * kNW + w; ut < n_tiles * kH; ut += P.G * kNW) {
       const int tile = ut / kH, head = ut - tile * kH;
       const int r0 = ins.row0 + 16 * tile, nq = min(16, nrows - 16 * tile);

@@ -88,7 +88,7 @@ struct ProgIter {
   __device__ __forceinline__ void reset(const Params& P) {
     phase = P.has_sample ? 0 : 1;
     layer = 0; op = OP_LN_QKV; group = 0; rot = 0;
-    row_group = (P.xn != nullptr && P.n_rows > kLnSplitMinRows && !(P.dbg_flags & 8)) ? 2 * kRowGroup : kRowGroup;
+    row_group = (P.xn != nullptr && P.n_rows > kLnSplitMinRows) ? 2 * kRowGroup : kRowGroup;
     n_groups = (P.n_rows + row_group - 1) / row_group;
     n_head_groups = (P.n_head_rows + kRowGroup - 1) / kRowGroup;
   }

@@ -527,12 +527,8 @@ __device__ void proj_splitk(const Params& P, int layer, int head, int rank, int 
       for (int tt = 0; tt < 2; ++tt)
       {
         long long* yp = P.y + (size_t)row * kD + col0 + 8 * tt;
-        if (P.dbg_flags & 4) {   // timing experiment only (wrong results): plain stores instead of atomics
-          *reinterpret_cast<longlong2*>(yp) = make_longlong2(to_fixed(acc[tt][0]), to_fixed(acc[tt][1]));
-        } else {
-          red_add_s64(yp, to_fixed((hh ? acc[tt][2] : acc[tt][0]) + add[tt].x));
-          red_add_s64(yp + 1, to_fixed((hh ? acc[tt][3] : acc[tt][1]) + add[tt].y));
-        }
+        red_add_s64(yp, to_fixed((hh ? acc[tt][2] : acc[tt][0]) + add[tt].x));
+        red_add_s64(yp + 1, to_fixed((hh ? acc[tt][3] : acc[tt][1]) + add[tt].y));
       }
     }
   }
@@ -619,9 +615,9 @@ __device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pi
 
 // ---- grid-wide barrier of this kernel ---------------------------------------------------------------------------------
 // Same counter protocol as ar_core.cuh grid_barrier.  Warp 0 also refills ring slots right after the arrival.
-// Acquire side: everything other CTAs write during the launch is read with ld.global.cg (L2, the coherence point)
-// and those loads are issued after the poll load has returned the final count, so no gpu-scope fence (and no L1
-// invalidate) is needed after the poll; TTS_AR_DBG bit 1 puts the fence back (A/B switch).
+// Acquire side: thread 0 polls relaxed and issues ONE fence.acq_rel.gpu once the count is complete; together with the
+// bar.sync that follows, the red.release of every producer CTA synchronizes-with the reads of all threads of this CTA
+// (PTX memory model: fence cumulativity through the CTA barrier).
 // `stage` (optional): `nstage` contiguous fp32 vectors of kD floats (LayerNorm gains / biases of the next phase) that
 // warps 4..7 copy into the start of the reduction buffer while thread 0 polls, so the LayerNorm after the barrier
 // reads them from shared memory instead of paying an L2 round trip between its statistics and its output.
@@ -662,7 +658,9 @@ __device__ __forceinline__ bool dec_grid_barrier(const Params& P, const Smem& sm
         }
       }
     }
-    if (P.dbg_flags & 2) fence_acq_rel_gpu();
+#ifndef TTS_DEC_NO_ACQUIRE_FENCE   // compile-time A/B only (scripts/ab.sh): the fence-free variant relies on every cross-CTA read being ld.cg
+    fence_acq_rel_gpu();   // acquire side: the consumers' reads after bar.sync are ordered after the producers' red.release
+#endif
   }
   consumer_sync();
   if (rec) P.prof[8192 + blockIdx.x * 8 + prof_slot + 3] = globaltimer_ns();
@@ -832,12 +830,13 @@ void launch_pack_projk(const void* src, int dtype, uint4* dst, cudaStream_t st) 
     pack_projk_kernel<__nv_bfloat16><<<512, 256, 0, st>>>((const __nv_bfloat16*)src, dst);
 }
 
-static cudaError_t decode_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attrs, int smem_bytes, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+static cudaError_t decode_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attrs, int smem_bytes, int device, bool cooperative,
+                                 cudaStream_t st) {
+  static unsigned long long attr_set = 0;   // one bit per device ordinal: the opt-in is per device
+  if (!(attr_set >> (device & 63) & 1ull)) {
     cudaError_t e = cudaFuncSetAttribute(ar_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
     if (e != cudaSuccess) return e;
-    attr_set = true;
+    attr_set |= 1ull << (device & 63);
   }
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(kDecCtas);
@@ -851,25 +850,24 @@ static cudaError_t decode_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* a
   attrs[1].id = cudaLaunchAttributeCooperative;
   attrs[1].val.cooperative = 1;
   cfg.attrs = attrs;
-  // TTS_AR_NOCOOP: plain cluster launch (profilers that cannot replay cooperative launches); the 128 CTAs are
-  // still co-resident on an otherwise idle B200 and every device-side wait is watchdogged.
-  cfg.numAttrs = getenv("TTS_AR_NOCOOP") ? 1 : 2;
+  // !cooperative: plain cluster launch (tts_ar_run.cu decode_cooperative: profilers cannot replay cooperative launches)
+  cfg.numAttrs = cooperative ? 2 : 1;
   return cudaSuccess;
 }
 
-cudaError_t launch_decode(const Params& P, int smem_bytes, cudaStream_t st) {
+cudaError_t launch_decode(const Params& P, int smem_bytes, int device, bool cooperative, cudaStream_t st) {
   cudaLaunchConfig_t cfg;
   cudaLaunchAttribute attrs[2];
-  cudaError_t e = decode_config(cfg, attrs, smem_bytes, st);
+  cudaError_t e = decode_config(cfg, attrs, smem_bytes, device, cooperative, st);
   if (e != cudaSuccess) return e;
   return cudaLaunchKernelEx(&cfg, ar_decode_kernel, P);
 }
 
 // Clusters of kClusterSize CTAs (1 CTA / SM at this shared-memory size) that can be co-resident; the kernel needs kDecClusters.
-int decode_max_clusters(int smem_bytes) {
+int decode_max_clusters(int smem_bytes, int device) {
   cudaLaunchConfig_t cfg;
   cudaLaunchAttribute attrs[2];
-  if (decode_config(cfg, attrs, smem_bytes, 0) != cudaSuccess) { cudaGetLastError(); return 0; }
+  if (decode_config(cfg, attrs, smem_bytes, device, true, 0) != cudaSuccess) { cudaGetLastError(); return 0; }
   cfg.numAttrs = 1;   // the occupancy query takes the cluster dimension only
   int n = 0;
   cudaError_t e = cudaOccupancyMaxActiveClusters(&n, ar_decode_kernel, &cfg);

@@ -180,6 +180,7 @@ __global__ void embed_rows_kernel(EmbedArgs a) {
   } else if (pos <= T + 2) {
     const int j = pos - 1;
     int tok = (j == 0) ? a.start_text : (j == T + 1 ? a.stop_text : a.text[(size_t)u * a.text_stride + (j - 1)]);
+    if ((tok < 0 || tok >= a.n_text_rows) && threadIdx.x == 0 && a.err_flag) *a.err_flag = 1;
     tok = min(max(tok, 0), a.n_text_rows - 1);
     e0 = a.text_emb + (size_t)tok * kD;
     e1 = a.text_pos + (size_t)j * kD;
@@ -189,6 +190,7 @@ __global__ void embed_rows_kernel(EmbedArgs a) {
     if (j == 0) tok = a.start_mel;
     else if (a.codes && j <= a.codes_len[u]) tok = a.codes[(size_t)u * a.codes_stride + (j - 1)];
     else tok = a.stop_mel;
+    if ((tok < 0 || tok >= a.n_mel_codes) && threadIdx.x == 0 && a.err_flag) *a.err_flag = 1;
     tok = min(max(tok, 0), a.n_mel_codes - 1);
     e0 = a.mel_emb + (size_t)tok * kD;
     e1 = a.mel_pos + (size_t)j * kD;
@@ -285,12 +287,12 @@ void launch_fill_i64(long long* p, size_t n, long long v, cudaStream_t st) {
   if (n) fill_i64_kernel<<<blocks, 256, 0, st>>>(p, n, v);
 }
 
-cudaError_t launch_program(const Params& P, int smem_bytes, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+cudaError_t launch_program(const Params& P, int smem_bytes, int device, cudaStream_t st) {
+  static unsigned long long attr_set = 0;   // one bit per device ordinal: the opt-in is per device (function handle)
+  if (!(attr_set >> (device & 63) & 1ull)) {
     cudaError_t e = cudaFuncSetAttribute(ar_program_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
     if (e != cudaSuccess) return e;
-    attr_set = true;
+    attr_set |= 1ull << (device & 63);
   }
   void* args[] = {const_cast<Params*>(&P)};
   return cudaLaunchCooperativeKernel((const void*)ar_program_kernel, dim3(P.G), dim3(kThreads), args, (size_t)smem_bytes, st);

@@ -18,6 +18,7 @@ struct EmbedArgs {
   const float* latent;     // [utts][1024]
   const float *text_emb, *text_pos, *mel_emb, *mel_pos;
   int start_text, stop_text, start_mel, stop_mel, n_text_rows, n_mel_codes;
+  int* err_flag;           // set to 1 when a token id is outside its embedding table (the reference raises IndexError)
 };
 
 void launch_pack_weight(const void* src, int dtype, uint4* dst, int K, int N, int n_tiles, int transposed, cudaStream_t st);
@@ -28,11 +29,11 @@ void launch_fixup_codes(long long* codes, int rows, int len, int stride, int sto
 void launch_reset_sampler(int n_seqs, int seen_words, uint32_t* seen, int* finished, int* gen_count, int* row_pos,
                           int* n_active, int start_mel, int* attn_cnt, int n_cnt, cudaStream_t st);
 void launch_fill_i64(long long* p, size_t n, long long v, cudaStream_t st);
-cudaError_t launch_program(const Params& P, int smem_bytes, cudaStream_t st);
+cudaError_t launch_program(const Params& P, int smem_bytes, int device, cudaStream_t st);
 int program_max_ctas_per_sm(int smem_bytes);
 // head-cluster decode kernel (ar_decode.cu)
 void launch_pack_projk(const void* src, int dtype, uint4* dst, cudaStream_t st);
-cudaError_t launch_decode(const Params& P, int smem_bytes, cudaStream_t st);
-int decode_max_clusters(int smem_bytes);
+cudaError_t launch_decode(const Params& P, int smem_bytes, int device, bool cooperative, cudaStream_t st);
+int decode_max_clusters(int smem_bytes, int device);
 
 }  // namespace tts

@@ -134,8 +134,9 @@ struct Params {
   int n_steps;
   unsigned long long* prof;   // nullable: CTA 0 stage timestamps (ns) of step prof_step: [2*pc] before / [2*pc+1] after the barrier
   int prof_step;
-  int dbg_flags;         // bring-up A/B switches (TTS_AR_DBG): bit 0 = per-CTA LayerNorm instead of the cluster-cooperative one; bit 1 = prompt-pass attention as one decode-shaped unit per (row, head) instead of 16-row mma tiles; bit 2 = 16-row tiles whatever the row count; bit 3 = 64-row GEMM instructions even when the A operand comes from L2
+  int attn_tiles_mode;   // interpreter prompt-mode attention (tts_ar_set_option "attn_tiles"): 0 auto, 1 per-(row, head) units, 2 always 16-row mma tiles
   int skip_last_model;   // generate(): the model is not run after the last sampled token
+  int ctx_row_major;     // dense passes (dense_pass.cu): attention context is bf16 [rows][1024], not mma A-fragment order
 };
 
 constexpr int kU4PerChunkP = kChunkBytes / 16;

@@ -137,14 +137,15 @@ static int create_impl(TtsArHandle* h) {
   DALLOC(h, h->d_bar, 4);
   DALLOC(h, h->d_watchdog, 4);
   DALLOC(h, h->d_steps_done, 4);
-  if (const char* e = getenv("TTS_AR_PROF_STEP")) {   // bring-up only: per-stage timestamps of one decode step
-    h->prof_step = atoi(e);
-    DALLOC(h, h->d_prof, 16384);
-  }
   DALLOC(h, h->d_in_latent, (size_t)c.max_utts * kD);
   DALLOC(h, h->d_in_text, (size_t)c.max_utts * std::max(c.max_text_len, 1));
   DALLOC(h, h->d_out_codes, (size_t)c.max_seqs * std::max(c.max_new_tokens, 1));
   TTS_CUDA(h, cudaMallocHost(&h->h_pinned_i, 64));
+  // staging for the per-call index uploads: page tables, lengths, row maps (all int32)
+  h->staging_bytes = sizeof(int) * ((size_t)pt_rows * (kMaxPagesPerSeg + 4) + 3 * (size_t)h->rows_cap + (size_t)h->logit_rows_cap +
+                                    (size_t)c.max_seqs * (kMaxPagesPerSeg + 2)) + 4096;
+  TTS_CUDA(h, cudaMallocHost(&h->h_staging, h->staging_bytes));
+  TTS_CUDA(h, cudaEventCreateWithFlags(&h->ev_staging, cudaEventDisableTiming));
   TTS_CUDA(h, cudaMallocHost(&h->h_pinned_codes, sizeof(long long) * (size_t)c.max_seqs * std::max(c.max_new_tokens, 1)));
   TTS_CUDA(h, cudaMallocHost(&h->h_pinned_latent, sizeof(float) * (size_t)c.max_utts * kD));
   TTS_CUDA(h, cudaMallocHost(&h->h_pinned_text, sizeof(int) * (size_t)c.max_utts * std::max(c.max_text_len, 1)));
@@ -157,12 +158,15 @@ static int create_impl(TtsArHandle* h) {
   const int smem1 = smem_total_bytes(1, smem_max_slots(1, h->smem_budget));
   if (program_max_ctas_per_sm(smem1) < 1) return fail(h, TTS_AR_ERR_DEVICE, "interpreter kernel does not fit on an SM");
   {
-    const char* e = getenv("TTS_AR_DECODE");   // "interp": force the interpreter kernel for decode (bring-up / A-B runs)
     const int smemd = smem_total_bytes(1, smem_max_slots(1, h->smem_budget));
-    const int ncl = decode_max_clusters(smemd);
-    h->use_cluster = !(e && std::string(e) == "interp") && ncl >= kDecClusters;
+    const int ncl = decode_max_clusters(smemd, c.device);
+    h->use_cluster = ncl >= kDecClusters;
     if (getenv("TTS_AR_VERBOSE")) fprintf(stderr, "[tts_ar] co-resident clusters of %d CTAs: %d (smem %d B) -> decode kernel: %s\n",
                                           kClusterSize, ncl, smemd, h->use_cluster ? "head-cluster" : "interpreter");
+  }
+  {
+    int rc = dense_create(h);   // K-major weight image + TMA tensor maps of the tcgen05 passes
+    if (rc) return rc;
   }
   TTS_CUDA(h, cudaDeviceSynchronize());
   return 0;
@@ -198,6 +202,8 @@ extern "C" void tts_ar_destroy(TtsArHandle* h) {
   if (h->h_pinned_codes) cudaFreeHost(h->h_pinned_codes);
   if (h->h_pinned_latent) cudaFreeHost(h->h_pinned_latent);
   if (h->h_pinned_text) cudaFreeHost(h->h_pinned_text);
+  if (h->h_staging) cudaFreeHost(h->h_staging);
+  if (h->ev_staging) cudaEventDestroy(h->ev_staging);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->ev2) cudaEventDestroy(h->ev2);
@@ -225,6 +231,7 @@ extern "C" int tts_ar_load_weights(TtsArHandle* h, const TtsArWeights* w, void* 
     launch_pack_weight(lw.c_fc_w, dt, const_cast<uint4*>(ld.w_fc), kD, kD4, kD4 / 8, 0, st);
     launch_pack_weight(lw.mlp_proj_w, dt, const_cast<uint4*>(ld.w_proj2), kD4, kD, kD / 8, 0, st);
     launch_pack_projk(lw.attn_proj_w, dt, const_cast<uint4*>(ld.w_projk), st);
+    dense_pack_layer(h, i, lw, dt, st);
     launch_to_f32(lw.ln_1_w, dt, const_cast<float*>(ld.ln1_g), kD, kD, st);
     launch_to_f32(lw.ln_1_b, dt, const_cast<float*>(ld.ln1_b), kD, kD, st);
     launch_to_f32(lw.ln_2_w, dt, const_cast<float*>(ld.ln2_g), kD, kD, st);
@@ -240,6 +247,7 @@ extern "C" int tts_ar_load_weights(TtsArHandle* h, const TtsArWeights* w, void* 
   for (const void* p : tops)
     if (!p) return fail(h, TTS_AR_ERR_BAD_ARG, "null weight pointer");
   launch_pack_weight(w->mel_head_w, dt, h->d_w_head, kD, c.n_mel_codes, h->v_tiles, 1, st);
+  dense_pack_head(h, w->mel_head_w, dt, st);
   launch_to_f32(w->mel_head_b, dt, h->d_b_head, c.n_mel_codes, h->v_stride, st);
   launch_to_f32(w->ln_f_w, dt, h->d_lnf_g, kD, kD, st);
   launch_to_f32(w->ln_f_b, dt, h->d_lnf_b, kD, kD, st);

@@ -1,10 +1,27 @@
 // tts_ar_host.h -- host-side state behind the opaque TtsArHandle (tts_ar.cu, tts_ar_run.cu).
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
+#include <cuda_bf16.h>
 #include <string>
 #include <vector>
 #include "../../include/tts_ar.h"
 #include "ar_launch.h"
+
+// K-major bf16 weight image + TMA tensor maps of the dense (tcgen05) passes: dense_pass.cu
+struct DenseW {
+  bool ok = false;
+  __nv_bfloat16* wt = nullptr;        // per layer: c_attn^T [3072][1024] | attn.c_proj^T [1024][1024] | c_fc^T [4096][1024] | mlp.c_proj^T [1024][4096]
+  __nv_bfloat16* wt_head = nullptr;   // mel_head [n_mel_codes][1024]
+  size_t per_layer = 0;
+  struct Layer {
+    __nv_bfloat16 *qkv, *proj, *fc, *proj2;
+    CUtensorMap m_qkv[2], m_proj[2], m_fc[2], m_proj2[2];   // [0]: 128-row boxes, [1]: 256-row boxes
+  };
+  std::vector<Layer> layers;
+  CUtensorMap m_head[2];
+  CUtensorMap a_xn, a_ctx, a_h;       // activation buffers as A operands (row-major bf16 in this path)
+};
 
 struct TtsArHandle {
   TtsArConfig cfg{};
@@ -36,6 +53,8 @@ struct TtsArHandle {
   float *d_b_head = nullptr, *d_lnf_g = nullptr, *d_lnf_b = nullptr, *d_fn_g = nullptr, *d_fn_b = nullptr;
   float *d_mel_emb = nullptr, *d_mel_pos = nullptr, *d_text_emb = nullptr, *d_text_pos = nullptr;
 
+  DenseW dense;
+
   // activations / cache (device)
   long long* d_y = nullptr;            // cluster decode kernel: attention-block accumulator [16][1024]
   bool use_cluster = false;         // 16 clusters of 8 CTAs can be co-resident (checked at create)
@@ -62,6 +81,14 @@ struct TtsArHandle {
   float* h_pinned_latent = nullptr;
   int* h_pinned_text = nullptr;
 
+  // pinned staging for the small host -> device index uploads of a call (tts_ar_run.cu Stager)
+  uint8_t* h_staging = nullptr;
+  size_t staging_bytes = 0;
+  cudaEvent_t ev_staging = nullptr;
+  bool staging_busy = false;
+  // explicit options (tts_ar_set_option)
+  int opt_decode_interp = 0, opt_dense_interp = 0, opt_attn_tiles = 0, opt_no_coop = 0;
+
   // per-call state
   bool prefilled = false;
   int n_utt = 0, n_cand = 0, n_seqs = 0;
@@ -79,12 +106,13 @@ struct TtsArHandle {
 namespace tts {
 int fail(TtsArHandle* h, int code, const std::string& msg);
 int cuda_fail(TtsArHandle* h, cudaError_t e, const char* what);
-// builds + uploads the decode program for h->n_seqs sequences; fills the Params fields it owns
-int build_decode_program(TtsArHandle* h, cudaStream_t st);
 void fill_common_params(TtsArHandle* h, Params& P);
-int run_prompt_pass(TtsArHandle* h, const std::vector<int>& seq_len, const std::vector<int>& row_utt,
-                    const std::vector<int>& row_pos, const std::vector<int>& head_rows, const std::vector<int>& latent_dst,
-                    float* latent_out, bool with_head, cudaStream_t st);
+bool decode_cooperative(TtsArHandle* h);
+// dense (tcgen05) passes: prompt pass and latent re-forward (dense_pass.cu)
+int dense_create(TtsArHandle* h);
+void dense_pack_layer(TtsArHandle* h, int l, const TtsArLayerWeights& lw, int dtype, cudaStream_t st);
+void dense_pack_head(TtsArHandle* h, const void* mel_head_w, int dtype, cudaStream_t st);
+int run_dense_pass(TtsArHandle* h, const Params& P, cudaStream_t st);
 }  // namespace tts
 
 #define TTS_CUDA(h, call)                                          \

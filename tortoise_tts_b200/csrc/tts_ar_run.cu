@@ -24,10 +24,8 @@ void fill_common_params(TtsArHandle* h, Params& P) {
   P.lnf_g = h->d_lnf_g; P.lnf_b = h->d_lnf_b; P.fn_g = h->d_fn_g; P.fn_b = h->d_fn_b;
   P.mel_emb = h->d_mel_emb; P.mel_pos = h->d_mel_pos;
   P.x = h->d_x; P.q = h->d_q; P.ctx = h->d_ctx; P.hbuf = h->d_h;
-  {
-    static const bool fused_ln = getenv("TTS_AR_LN_FUSED") != nullptr;   // bring-up A/B: every CTA normalises all rows itself
-    P.xn = fused_ln ? nullptr : h->d_xn;
-  }
+  P.xn = h->d_xn;
+  P.attn_tiles_mode = h->opt_attn_tiles;
   P.logits = h->d_logits; P.cur_latent = h->d_cur_latent;
   P.logits_pf = h->d_logits; P.cur_latent_pf = h->d_cur_latent;
   P.kv = h->d_kv; P.n_pages = h->n_pages;
@@ -47,41 +45,67 @@ static int mt_max_for(int n_rows) {
   return m <= 1 ? 1 : (m == 2 ? 2 : 4);
 }
 
-int build_decode_program(TtsArHandle* h, cudaStream_t st) {
-  (void)st;
-  h->dec_mt_max = mt_max_for(h->n_seqs);   // the instruction sequence itself is generated on the device (ProgIter)
-  return 0;
-}
-
 static int launch(TtsArHandle* h, Params& P, cudaStream_t st, bool cluster = false) {
   P.n_slots = smem_max_slots(P.mt_max, h->smem_budget);
   if (P.n_slots < 2) return fail(h, TTS_AR_ERR_DEVICE, "not enough shared memory for the weight ring");
   TTS_CUDA(h, cudaMemsetAsync(h->d_bar, 0, sizeof(unsigned int), st));
   cudaError_t e;
-  if (const char* e = getenv("TTS_AR_DBG")) P.dbg_flags = atoi(e);   // bring-up A/B switches (ar_params.h dbg_flags)
   if (cluster) {
     P.G = kDecCtas;
     P.y = h->d_y;
     P.mt_max = 1;
     P.n_slots = smem_max_slots(1, h->smem_budget);
-    if (const char* e = getenv("TTS_AR_SLOTS")) P.n_slots = std::max(2, std::min(P.n_slots, atoi(e)));   // bring-up: ring depth
     TTS_CUDA(h, cudaMemsetAsync(h->d_y, 0, sizeof(long long) * kDecRows * kD, st));
-    e = launch_decode(P, smem_total_bytes(1, P.n_slots), st);
+    e = launch_decode(P, smem_total_bytes(1, P.n_slots), h->cfg.device, decode_cooperative(h), st);
     if (e != cudaSuccess) return cuda_fail(h, e, "cudaLaunchKernelEx(ar_decode_kernel)");
     h->launches += 1;
     return 0;
   }
-  e = launch_program(P, smem_total_bytes(P.mt_max, P.n_slots), st);
+  e = launch_program(P, smem_total_bytes(P.mt_max, P.n_slots), h->cfg.device, st);
   if (e != cudaSuccess) return cuda_fail(h, e, "cudaLaunchCooperativeKernel(ar_program_kernel)");
   h->launches += 1;
   return 0;
 }
 
+// Host -> device upload of small index arrays through the handle's pinned staging area (no pageable copies, so no
+// synchronisation on the call path).  The area is recycled per call: before the first write of a call the previous
+// call's copies must have been consumed (an event wait that is normally already satisfied).
+struct Stager {
+  TtsArHandle* h;
+  cudaStream_t st;
+  size_t used = 0;
+  int rc = 0;
+  Stager(TtsArHandle* h_, cudaStream_t st_) : h(h_), st(st_) {
+    if (h->staging_busy) {
+      cudaError_t e = cudaEventSynchronize(h->ev_staging);
+      if (e != cudaSuccess) rc = cuda_fail(h, e, "cudaEventSynchronize(staging)");
+      h->staging_busy = false;
+    }
+  }
+  int put(void* dst, const void* src, size_t bytes) {
+    if (rc) return rc;
+    const size_t a = (bytes + 15) & ~(size_t)15;
+    if (used + a > h->staging_bytes) return rc = fail(h, TTS_AR_ERR_CAPACITY, "host staging area too small");
+    memcpy(h->h_staging + used, src, bytes);
+    cudaError_t e = cudaMemcpyAsync(dst, h->h_staging + used, bytes, cudaMemcpyHostToDevice, st);
+    used += a;
+    if (e != cudaSuccess) rc = cuda_fail(h, e, "cudaMemcpyAsync(staging)");
+    return rc;
+  }
+  int done() {
+    if (rc) return rc;
+    cudaError_t e = cudaEventRecord(h->ev_staging, st);
+    if (e != cudaSuccess) return rc = cuda_fail(h, e, "cudaEventRecord(staging)");
+    h->staging_busy = true;
+    return 0;
+  }
+};
+
 // Prompt-shaped causal pass: sequences laid out back to back as rows; every sequence is its own "utterance"
 // whose KV lives in prefix pages.  Used by tts_ar_prefill (with_head) and tts_ar_forward_latents (latent_out).
-int run_prompt_pass(TtsArHandle* h, const std::vector<int>& seq_len, const std::vector<int>& row_utt,
+int run_prompt_pass(TtsArHandle* h, Stager& sg, const std::vector<int>& seq_len, const std::vector<int>& row_utt,
                     const std::vector<int>& row_pos, const std::vector<int>& head_rows, const std::vector<int>& latent_dst,
-                    float* latent_out, bool with_head, cudaStream_t st) {
+                    bool with_head, cudaStream_t st) {
   const int n_seq = (int)seq_len.size();
   const int n_rows = (int)row_utt.size();
   if (n_rows > h->rows_cap) return fail(h, TTS_AR_ERR_CAPACITY, "prompt rows exceed capacity");
@@ -94,18 +118,28 @@ int run_prompt_pass(TtsArHandle* h, const std::vector<int>& seq_len, const std::
     for (int p = 0; p < np; ++p) pt[(size_t)i * kMaxPagesPerSeg + p] = next_page++;
   }
   if (next_page > h->n_pages) return fail(h, TTS_AR_ERR_CAPACITY, "KV page pool exhausted");
-  const int n_head_rows = with_head ? (int)head_rows.size() : 0;
-  TTS_CUDA(h, cudaMemcpyAsync(h->d_prefix_pt, pt.data(), sizeof(int) * pt.size(), cudaMemcpyHostToDevice, st));
-  TTS_CUDA(h, cudaMemcpyAsync(h->d_utt_plen, seq_len.data(), sizeof(int) * n_seq, cudaMemcpyHostToDevice, st));
-  TTS_CUDA(h, cudaMemcpyAsync(h->d_pf_row_utt, row_utt.data(), sizeof(int) * n_rows, cudaMemcpyHostToDevice, st));
-  TTS_CUDA(h, cudaMemcpyAsync(h->d_pf_row_pos, row_pos.data(), sizeof(int) * n_rows, cudaMemcpyHostToDevice, st));
+  sg.put(h->d_prefix_pt, pt.data(), sizeof(int) * pt.size());
+  sg.put(h->d_utt_plen, seq_len.data(), sizeof(int) * n_seq);
+  sg.put(h->d_pf_row_utt, row_utt.data(), sizeof(int) * n_rows);
+  sg.put(h->d_pf_row_pos, row_pos.data(), sizeof(int) * n_rows);
   if (with_head)
-    TTS_CUDA(h, cudaMemcpyAsync(h->d_head_rows, head_rows.data(), sizeof(int) * n_head_rows, cudaMemcpyHostToDevice, st));
+    sg.put(h->d_head_rows, head_rows.data(), sizeof(int) * head_rows.size());
   else
-    TTS_CUDA(h, cudaMemcpyAsync(h->d_latent_dst, latent_dst.data(), sizeof(int) * n_rows, cudaMemcpyHostToDevice, st));
+    sg.put(h->d_latent_dst, latent_dst.data(), sizeof(int) * n_rows);
+  if (sg.rc) return sg.rc;
   TTS_CUDA(h, cudaMemsetAsync(h->d_plan, 0, sizeof(int) * 4, st));   // plan[0] = 0: direct (row, head) units
-  TTS_CUDA(h, cudaStreamSynchronize(st));                             // local pageable buffers above
   return 0;
+}
+
+// Launch-attribute choice for the head-cluster kernel: cooperative (co-residency checked by the driver) unless the
+// caller opted out or a profiler that cannot replay cooperative launches is injected into this process (Nsight Compute
+// sets these variables in the target's environment); the 128 CTAs of a plain cluster launch are still co-resident on an
+// otherwise idle B200 and every device-side wait is watchdogged.
+bool decode_cooperative(TtsArHandle* h) {
+  if (h->opt_no_coop) return false;
+  static const bool profiled = getenv("NV_COMPUTE_PROFILER_PERFWORKS_DIR") != nullptr || getenv("CUDA_INJECTION64_PATH") != nullptr ||
+                               getenv("NV_NSIGHT_INJECTION_TRANSPORT_TYPE") != nullptr;
+  return !profiled;
 }
 
 }  // namespace tts
@@ -138,15 +172,18 @@ extern "C" int tts_ar_prefill(TtsArHandle* h, const float* latent, const int32_t
   const int n_rows = (int)row_utt.size();
   h->prefilled = false;
   TTS_CUDA(h, cudaEventRecord(h->ev0, st));
-  TTS_CUDA(h, cudaMemcpyAsync(h->d_text_len, text_len, sizeof(int) * n_utt, cudaMemcpyHostToDevice, st));
-  rc = run_prompt_pass(h, seq_len, row_utt, row_pos, head_rows, none, nullptr, true, st);
+  TTS_CUDA(h, cudaMemsetAsync(h->d_watchdog, 0, 2 * sizeof(int), st));   // watchdog + bad-token flags of the previous call
+  Stager sg(h, st);
+  if (sg.rc) return sg.rc;
+  sg.put(h->d_text_len, text_len, sizeof(int) * n_utt);
+  rc = run_prompt_pass(h, sg, seq_len, row_utt, row_pos, head_rows, none, true, st);
   if (rc) return rc;
   EmbedArgs ea{};
   ea.x = h->d_x; ea.row_utt = h->d_pf_row_utt; ea.row_pos_in = h->d_pf_row_pos; ea.text_len = h->d_text_len;
   ea.text = text; ea.text_stride = text_stride; ea.codes = nullptr; ea.codes_len = h->d_codes_len; ea.codes_stride = 0;
   ea.latent = latent; ea.text_emb = h->d_text_emb; ea.text_pos = h->d_text_pos; ea.mel_emb = h->d_mel_emb; ea.mel_pos = h->d_mel_pos;
   ea.start_text = c.start_text_token; ea.stop_text = c.stop_text_token; ea.start_mel = c.start_mel_token; ea.stop_mel = c.stop_mel_token;
-  ea.n_text_rows = c.n_text_rows; ea.n_mel_codes = c.n_mel_codes;
+  ea.n_text_rows = c.n_text_rows; ea.n_mel_codes = c.n_mel_codes; ea.err_flag = h->d_watchdog + 1;
   launch_embed_rows(ea, n_rows, st);
   h->launches += 1;
   Params P;
@@ -157,7 +194,7 @@ extern "C" int tts_ar_prefill(TtsArHandle* h, const float* latent, const int32_t
   P.has_sample = 0; P.n_rows = n_rows; P.tail = 1; P.n_head_rows = n_utt;
   P.n_steps = 1;
   P.n_seqs = 0;
-  rc = launch(h, P, st);
+  rc = h->opt_dense_interp ? launch(h, P, st) : run_dense_pass(h, P, st);
   if (rc) return rc;
   // sequences: utterance-major, candidates adjacent (repeat_interleave, stream_generator.py:618-623)
   h->n_utt = n_utt; h->n_cand = n_cand; h->n_seqs = n_utt * n_cand;
@@ -170,13 +207,14 @@ extern "C" int tts_ar_prefill(TtsArHandle* h, const float* latent, const int32_t
     for (int p = 0; p < h->nqp; ++p) priv[(size_t)s * kMaxPagesPerSeg + p] = next_page++;
   }
   if (next_page > h->n_pages) return fail(h, TTS_AR_ERR_CAPACITY, "KV page pool exhausted");
-  TTS_CUDA(h, cudaMemcpyAsync(h->d_seq_utt, seq_utt.data(), sizeof(int) * h->n_seqs, cudaMemcpyHostToDevice, st));
-  TTS_CUDA(h, cudaMemcpyAsync(h->d_priv_pt, priv.data(), sizeof(int) * priv.size(), cudaMemcpyHostToDevice, st));
+  sg.put(h->d_seq_utt, seq_utt.data(), sizeof(int) * h->n_seqs);
+  sg.put(h->d_priv_pt, priv.data(), sizeof(int) * priv.size());
+  rc = sg.done();
+  if (rc) return rc;
   launch_reset_sampler(h->n_seqs, h->seen_words, h->d_seen, h->d_finished, h->d_gen_count, h->d_seq_pos, h->d_n_active,
                        c.start_mel_token, h->d_attn_cnt, h->n_seqs * kH, st);
   h->launches += 1;
-  rc = build_decode_program(h, st);   // synchronises: seq_utt / priv are local
-  if (rc) return rc;
+  h->dec_mt_max = mt_max_for(h->n_seqs);
   TTS_CUDA(h, cudaEventRecord(h->ev1, st));
   TTS_CUDA(h, cudaGetLastError());
   h->tokens_done = 0;
@@ -215,8 +253,7 @@ static int run_steps(TtsArHandle* h, const TtsArSampling* s, int n_steps, bool s
   // 17..32 sequences: two consecutive launches of the 16-row head-cluster kernel (670 us/step each) beat one pass of the
   // interpreter over 32 rows (1630 us/step).  Every per-sequence array is a pointer offset; sequences are independent and
   // the Philox key is the global sequence index, so the result is bit-identical to two separate 16-candidate calls.
-  static const bool no_groups = getenv("TTS_AR_NO_GROUPS") != nullptr;
-  h->grouped = h->use_cluster && !no_groups && h->n_seqs > kDecRows && h->n_seqs <= 2 * kDecRows;
+  h->grouped = h->use_cluster && !h->opt_decode_interp && h->n_seqs > kDecRows && h->n_seqs <= 2 * kDecRows;
   int rc = 0;
   if (h->grouped) {
     const int stash = 2 * kDecRows;            // logit rows [32, 32 + n_utt): the prompt-pass rows, kept for group 1
@@ -244,7 +281,7 @@ static int run_steps(TtsArHandle* h, const TtsArSampling* s, int n_steps, bool s
       rc = launch(h, Q, st, true);
     }
   } else {
-    rc = launch(h, P, st, h->use_cluster && h->n_seqs <= kDecRows);
+    rc = launch(h, P, st, h->use_cluster && !h->opt_decode_interp && h->n_seqs <= kDecRows);
   }
   if (rc) return rc;
   // SURVEY.md 8(d) algorithmic bytes, assuming every sequence stays live (exact under ignore_eos)
@@ -296,6 +333,7 @@ extern "C" int tts_ar_sync_result(TtsArHandle* h, TtsArStats* out, void* stream)
   TTS_CUDA(h, cudaSetDevice(h->cfg.device));
   TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[0], h->d_steps_done, sizeof(int), cudaMemcpyDeviceToHost, st));
   TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[1], h->d_watchdog, sizeof(int), cudaMemcpyDeviceToHost, st));
+  TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[3], h->d_watchdog + 1, sizeof(int), cudaMemcpyDeviceToHost, st));
   TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[2], h->d_n_active, sizeof(int), cudaMemcpyDeviceToHost, st));
   if (h->grouped) {   // per-group counters: the call ran until its slowest group finished
     TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[4], h->d_steps_done + 1, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -321,7 +359,13 @@ extern "C" int tts_ar_sync_result(TtsArHandle* h, TtsArStats* out, void* stream)
     if (cudaEventElapsedTime(&b, h->ev0, h->ev2) == cudaSuccess) out->last_device_ms = b;
     cudaGetLastError();
   }
-  if (out->watchdog) return fail(h, TTS_AR_ERR_WATCHDOG, "device-side wait timed out (watchdog); results are invalid");
+  if (out->watchdog || h->h_pinned_i[3]) {
+    // reported once: the flags are cleared so that the handle stays usable (they are also cleared by the next prefill)
+    cudaMemsetAsync(h->d_watchdog, 0, 2 * sizeof(int), st);
+    if (out->watchdog) return fail(h, TTS_AR_ERR_WATCHDOG, "device-side wait timed out (watchdog); results are invalid");
+    // the reference's nn.Embedding raises IndexError on such an id (unified_voice.py:642, 205)
+    return fail(h, TTS_AR_ERR_BAD_ARG, "a text or mel token id is outside its embedding table");
+  }
   return 0;
 }
 
@@ -334,6 +378,7 @@ extern "C" int tts_ar_forward_latents(TtsArHandle* h, const float* latent, const
   const TtsArConfig& c = h->cfg;
   cudaStream_t st = (cudaStream_t)stream;
   h->prefilled = false;   // the KV pool and activations are reused: generation state is gone
+  TTS_CUDA(h, cudaMemsetAsync(h->d_watchdog, 0, 2 * sizeof(int), st));
   int i0 = 0;
   while (i0 < n) {
     // sub-batch that fits the row capacity
@@ -365,9 +410,13 @@ extern "C" int tts_ar_forward_latents(TtsArHandle* h, const float* latent, const
         latent_dst.push_back((j >= 0 && j < M) ? (i0 + b) * codes_stride + j : -1);
       }
     }
-    TTS_CUDA(h, cudaMemcpyAsync(h->d_text_len, text_len + i0, sizeof(int) * nb, cudaMemcpyHostToDevice, st));
-    TTS_CUDA(h, cudaMemcpyAsync(h->d_codes_len, codes_len + i0, sizeof(int) * nb, cudaMemcpyHostToDevice, st));
-    rc = run_prompt_pass(h, seq_len, row_utt, row_pos, none, latent_dst, out, false, st);
+    Stager sg(h, st);
+    if (sg.rc) return sg.rc;
+    sg.put(h->d_text_len, text_len + i0, sizeof(int) * nb);
+    sg.put(h->d_codes_len, codes_len + i0, sizeof(int) * nb);
+    rc = run_prompt_pass(h, sg, seq_len, row_utt, row_pos, none, latent_dst, false, st);
+    if (rc) return rc;
+    rc = sg.done();
     if (rc) return rc;
     const int n_rows = (int)row_utt.size();
     EmbedArgs ea{};
@@ -377,7 +426,7 @@ extern "C" int tts_ar_forward_latents(TtsArHandle* h, const float* latent, const
     ea.latent = latent + (size_t)i0 * kD;
     ea.text_emb = h->d_text_emb; ea.text_pos = h->d_text_pos; ea.mel_emb = h->d_mel_emb; ea.mel_pos = h->d_mel_pos;
     ea.start_text = c.start_text_token; ea.stop_text = c.stop_text_token; ea.start_mel = c.start_mel_token; ea.stop_mel = c.stop_mel_token;
-    ea.n_text_rows = c.n_text_rows; ea.n_mel_codes = c.n_mel_codes;
+    ea.n_text_rows = c.n_text_rows; ea.n_mel_codes = c.n_mel_codes; ea.err_flag = h->d_watchdog + 1;
     launch_embed_rows(ea, n_rows, st);
     h->launches += 1;
     Params P;
@@ -388,7 +437,7 @@ extern "C" int tts_ar_forward_latents(TtsArHandle* h, const float* latent, const
     P.has_sample = 0; P.n_rows = n_rows; P.tail = 2; P.n_head_rows = 0;
     P.n_steps = 1;
     P.latent_out = out;
-    rc = launch(h, P, st);
+    rc = h->opt_dense_interp ? launch(h, P, st) : run_dense_pass(h, P, st);
     if (rc) return rc;
     i0 = i1;
   }
@@ -399,7 +448,7 @@ extern "C" int tts_ar_forward_latents(TtsArHandle* h, const float* latent, const
 extern "C" int tts_ar_inference_speech_host(TtsArHandle* h, const float* latent_host, const int32_t* text_host,
                                             int32_t text_stride, const int32_t* text_len, int32_t n_utt, int32_t n_cand,
                                             const TtsArSampling* s, int32_t max_new, int64_t* out_codes_host,
-                                            int32_t* steps_run) {
+                                            int32_t* steps_run, void* stream) {
   int rc = check_ready(h, false);
   if (rc) return rc;
   const TtsArConfig& c = h->cfg;
@@ -407,7 +456,7 @@ extern "C" int tts_ar_inference_speech_host(TtsArHandle* h, const float* latent_
     return fail(h, TTS_AR_ERR_BAD_ARG, "bad inference_speech argument");
   if (n_utt > c.max_utts || n_utt * n_cand > c.max_seqs || text_stride > std::max(c.max_text_len, 1) || max_new > c.max_new_tokens)
     return fail(h, TTS_AR_ERR_CAPACITY, "batch exceeds capacity");
-  cudaStream_t st = 0;   // legacy default stream of this device
+  cudaStream_t st = (cudaStream_t)stream;
   const size_t nb_lat = sizeof(float) * (size_t)n_utt * kD, nb_txt = sizeof(int) * (size_t)n_utt * text_stride;
   memcpy(h->h_pinned_latent, latent_host, nb_lat);
   memcpy(h->h_pinned_text, text_host, nb_txt);
@@ -454,5 +503,34 @@ extern "C" int tts_ar_debug_copy(TtsArHandle* h, const char* name, void* dst, ui
   else if (n == "prof") src = h->d_prof;
   else return fail(h, TTS_AR_ERR_BAD_ARG, "unknown debug buffer");
   TTS_CUDA(h, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return 0;
+}
+
+extern "C" int tts_ar_set_option(TtsArHandle* h, const char* name, int32_t value) {
+  if (!h || !name) return TTS_AR_ERR_BAD_ARG;
+  const std::string n(name);
+  if (n == "decode_kernel") {            // 0: head-cluster kernels when co-resident (default); 1: the interpreter kernel
+    if (value != 0 && value != 1) return fail(h, TTS_AR_ERR_BAD_ARG, "decode_kernel: 0 (auto) or 1 (interpreter)");
+    h->opt_decode_interp = value;
+  } else if (n == "dense_kernel") {      // 0: tcgen05 pipeline (default); 1: the interpreter kernel in prompt mode
+    if (value != 0 && value != 1) return fail(h, TTS_AR_ERR_BAD_ARG, "dense_kernel: 0 (tcgen05) or 1 (interpreter)");
+    h->opt_dense_interp = value;
+  } else if (n == "attn_tiles") {        // prompt-pass attention: 0 auto, 1 one unit per (row, head), 2 always 16-row tiles
+    if (value < 0 || value > 2) return fail(h, TTS_AR_ERR_BAD_ARG, "attn_tiles: 0, 1 or 2");
+    h->opt_attn_tiles = value;
+  } else if (n == "cooperative_launch") {   // 1 (default): cooperative cluster launch; 0: plain cluster launch
+    h->opt_no_coop = value ? 0 : 1;
+  } else if (n == "prof_step") {         // per-stage timestamps of one decode step (scripts/stage_prof.py); -1 off
+    h->prof_step = value;
+    if (value >= 0 && !h->d_prof) {
+      void* p = nullptr;
+      cudaError_t e = cudaMalloc(&p, 16384 * sizeof(unsigned long long));
+      if (e != cudaSuccess) return cuda_fail(h, e, "cudaMalloc(prof)");
+      h->allocs.push_back(p);
+      h->d_prof = reinterpret_cast<unsigned long long*>(p);
+    }
+  } else {
+    return fail(h, TTS_AR_ERR_BAD_ARG, "unknown option");
+  }
   return 0;
 }

@@ -81,23 +81,54 @@ class UnifiedVoiceB200:
         except Exception:
             pass
 
+    @staticmethod
+    def module_weights(module):
+        """{reference state_dict key: tensor} for the AR path, collected by walking `named_modules()` and READING the
+        `.weight` / `.bias` attributes.  With the reference's LoRA active (`torch.nn.utils.parametrize`, reference
+        lora.py:163-195) `state_dict()` holds `...parametrizations.weight.original` (the un-merged base weight) while
+        the attribute returns the merged value W + (B @ A) * scale; a swapped-in `LoRAConv1d` / `LoRALinear`
+        (lora.py:21-140) keeps `.weight` as the base and carries `lora_A`, `lora_B`, `scaling`, `merged`: those are merged
+        here the way the module's own `forward` applies them."""
+        import torch.nn as nn
+        out = {}
+        for name, mod in module.named_modules():
+            if name.startswith("inference_model") or ".parametrizations" in name:
+                continue   # inference_model shares gpt / embeddings / heads (unified_voice.py:453-487): same tensors
+            for attr in ("weight", "bias"):
+                t = getattr(mod, attr, None)
+                if not isinstance(t, torch.Tensor):
+                    continue
+                t = t.detach()
+                if attr == "weight" and hasattr(mod, "lora_A") and hasattr(mod, "lora_B") and not getattr(mod, "merged", False) \
+                        and getattr(mod, "enabled", True):
+                    a, b = mod.lora_A.detach(), mod.lora_B.detach()
+                    scale = float(getattr(mod, "scaling", getattr(mod, "scale", 1.0)))
+                    delta = (b @ a) * scale if b.shape[0] == t.shape[0] else ((b @ a) * scale).t()
+                    if delta.shape == t.shape:
+                        t = t + delta.to(t.dtype)
+                out[f"{name}.{attr}" if name else attr] = t
+        return out
+
     @classmethod
     def from_module(cls, module, **kw):
-        """Snapshot a reference `UnifiedVoice` nn.Module (reading `.weight` returns LoRA-merged values when
-        parametrizations are active, reference lora.py:163-195)."""
+        """Snapshot a reference `UnifiedVoice` nn.Module; LoRA-merged values are taken (see `module_weights`)."""
         g = ARGeometry(layers=module.layers, model_dim=module.model_dim, heads=module.heads,
                        max_text_tokens=module.max_text_tokens, max_mel_tokens=module.max_mel_tokens,
                        max_conditioning_inputs=module.max_conditioning_inputs,
                        number_text_tokens=module.number_text_tokens, start_text_token=module.start_text_token,
                        stop_text_token=module.stop_text_token, number_mel_codes=module.number_mel_codes,
                        start_mel_token=module.start_mel_token, stop_mel_token=module.stop_mel_token)
-        return cls(module.state_dict(), geometry=g, **kw)
+        return cls(cls.module_weights(module), geometry=g, **kw)
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
     def _check(self, rc, what):
         _lib.check(self.lib, self.handle, rc, what)
+
+    def set_option(self, name, value):
+        """Explicit per-handle option (include/tts_ar.h tts_ar_set_option)."""
+        self._check(self.lib.tts_ar_set_option(self.handle, name.encode(), int(value)), f"tts_ar_set_option({name})")
 
     def load_state_dict(self, sd):
         """Re-snapshot the weights (call after the module's load_state_dict or a LoRA toggle)."""
@@ -295,6 +326,17 @@ class UnifiedVoiceB200:
                 text_first=True, raw_mels=None, return_attentions=False, return_latent=False, clip_inputs=True):
         if not return_latent or not text_first or raw_mels is not None or types is not None or return_attentions:
             raise NotImplementedError("only forward(..., return_latent=True, text_first=True) is on the AR inference path")
+        n = mel_codes.shape[0]
+        # the reference caller passes lengths as [n] or [n, 1] (inference.py:371-379: wav_lengths.repeat(candidates, 1));
+        # set_mel_padding / the clipping below are per row (unified_voice.py:494-506, 565-571)
+        wav_lengths = torch.as_tensor(wav_lengths).reshape(-1)
+        text_lengths = torch.as_tensor(text_lengths).reshape(-1)
+        if wav_lengths.numel() == 1:
+            wav_lengths = wav_lengths.expand(n)
+        if text_lengths.numel() == 1:
+            text_lengths = text_lengths.expand(n)
+        if wav_lengths.numel() != n or text_lengths.numel() != n:
+            raise ValueError("text_lengths / wav_lengths must have one entry per row of mel_codes")
         if clip_inputs:
             max_text_len = int(text_lengths.max())
             text_inputs = text_inputs[:, :max_text_len]
@@ -307,6 +349,7 @@ class UnifiedVoiceB200:
         mel_lengths = torch.div(wav_lengths.to(self.device), 1024, rounding_mode="trunc")
         idx = torch.arange(M, device=self.device)[None, :]
         codes = torch.where(idx >= (mel_lengths[:, None] + 1), torch.full_like(codes, self.stop_mel_token), codes)
+        assert codes.shape == (n, M)
         codes = codes.to(torch.int32).contiguous()
         lat = speech_conditioning_latent.detach().to(device=self.device, dtype=torch.float32).contiguous()
         txt = text_inputs.detach().to(device=self.device, dtype=torch.int32).contiguous()
@@ -332,7 +375,7 @@ class UnifiedVoiceB200:
         steps = C.c_int32(0)
         self._check(self.lib.tts_ar_inference_speech_host(self.handle, _ptr(lat), _ptr(txt), T, lens, U,
                                                           int(num_return_sequences), C.byref(s), max_new, _ptr(out),
-                                                          C.byref(steps)), "tts_ar_inference_speech_host")
+                                                          C.byref(steps), self._stream()), "tts_ar_inference_speech_host")
         return out[:, : steps.value]
 
 
