@@ -649,7 +649,12 @@ __device__ __forceinline__ bool dec_grid_barrier(const Params& P, const Smem& sm
     const uint32_t target = epoch * (uint32_t)P.G;
     const long long t0 = clock64();
     uint32_t spins = 0;
-    while (ld_relaxed_u32(P.bar_counter) < target) {
+#ifdef TTS_DEC_ACQUIRE_POLL
+#define TTS_DEC_POLL ld_acquire_u32
+#else
+#define TTS_DEC_POLL ld_relaxed_u32
+#endif
+    while (TTS_DEC_POLL(P.bar_counter) < target) {
       if ((++spins & 255u) == 0) {
         if (c->abort_flag || __ldcg(P.watchdog) || clock64() - t0 > kWatchdogCycles) {
           c->abort_flag = 1;
@@ -658,7 +663,7 @@ __device__ __forceinline__ bool dec_grid_barrier(const Params& P, const Smem& sm
         }
       }
     }
-#ifndef TTS_DEC_NO_ACQUIRE_FENCE   // compile-time A/B only (scripts/ab.sh): the fence-free variant relies on every cross-CTA read being ld.cg
+#if !defined(TTS_DEC_NO_ACQUIRE_FENCE) && !defined(TTS_DEC_ACQUIRE_POLL)   // compile-time A/B only (scripts/ab.sh): the fence-free variant relies on every cross-CTA read being ld.cg
     fence_acq_rel_gpu();   // acquire side: the consumers' reads after bar.sync are ordered after the producers' red.release
 #endif
   }

@@ -149,7 +149,7 @@ __device__ __forceinline__ void tc_epilogue(const TcGemmArgs& g, int row, int co
   }
   if (EPI == TC_EPI_STORE) {
     float* o = g.out_f32 + (size_t)row * g.ldo + col;
-    if (col + 32 <= g.N) {
+    if (col + 32 <= g.N && (g.ldo & 3) == 0) {   // 16-byte aligned rows (the product's logits rows are: v_stride % 8 == 0)
 #pragma unroll
       for (int i = 0; i < 32; i += 4) *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
     } else {
