@@ -104,6 +104,8 @@ typedef struct {
   float typical_mass;           /* TypicalLogitsWarper(mass) of unified_voice.py:47-75, run as a logits PROCESSOR (:659): after
                                    the repetition penalty, before temperature / top-k / top-p, also in greedy mode;
                                    outside (0,1) = off (0 in zero-initialised structs) */
+  const int64_t* seq_indices;   /* dev int64 [n_seq] or NULL: global index of every local sequence, for shards that are not
+                                   contiguous in the global order (length-balanced utterance shards); overrides seq_index_base */
 } TtsArSampling;
 
 typedef struct {

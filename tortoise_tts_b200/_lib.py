@@ -44,7 +44,7 @@ class TtsArSampling(C.Structure):
     _fields_ = [("struct_size", C.c_int32), ("do_sample", C.c_int32), ("temperature", C.c_float),
                 ("top_k", C.c_int32), ("top_p", C.c_float), ("repetition_penalty", C.c_float),
                 ("seed", C.c_uint64), ("seq_index_base", C.c_int64), ("ignore_eos", C.c_int32),
-                ("typical_mass", C.c_float)]
+                ("typical_mass", C.c_float), ("seq_indices", C.c_void_p)]
 
 
 class TtsArStats(C.Structure):

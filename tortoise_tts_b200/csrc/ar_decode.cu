@@ -1,13 +1,21 @@
-// ar_decode.cu -- the head-cluster decode kernel: the sample loop for <= 16 live sequences.
+// ar_decode.cu -- the head-cluster decode kernels: the sample loop for <= 16, <= 32 or <= 64 live sequences per launch.
 //
 // Same stages as the interpreter (ar_kernels.cu) but with 3 grid-wide barriers per GPT-2 block instead of 5:
-// 32 thread-block clusters of 4 CTAs, cluster c owns attention head c >> 1 for 8 of the 16 rows, so
+// 32 thread-block clusters of 4 CTAs, cluster c owns attention head c >> 1 for one half of the launch's rows, so
 //     ln_1 -> c_attn (q,k,v columns of the head) -> [cluster barrier] -> attention of the head ->
 //     [cluster barrier] -> split-K attn.c_proj (rows 64h..64h+63 of the weight) -> red.add into y
-// runs without leaving the cluster (phase A); the 16 per-head partial products are summed in L2 by
-// 64-bit integer atomics in 2^-32 fixed point (order-independent => deterministic) into the zeroed accumulator y (head 0 also adds the residual x and the bias).
-// Phase B = ln_2 -> c_fc -> gelu_new (N split over the 128 CTAs), phase C = mlp.c_proj: x = y + . ; y = 0.
-// Weights stream through the same bulk-copy ring as in the interpreter, ungated by any barrier.
+// runs without leaving the cluster (phase A); the 16 per-head partial products are summed in L2 by 64-bit integer
+// atomics in 2^-32 fixed point (order-independent => deterministic) into the accumulator y, which the previous stage
+// left initialised to x + bias (the residual), so all 16 heads do the same work.
+// Phase B = ln_2 -> c_fc -> gelu_new (N split over the 128 CTAs), phase C = mlp.c_proj: x = y + . ; y = x + next bias.
+// Weights stream through the same bulk-copy ring as in the interpreter, ungated by any barrier, and every streamed
+// chunk is multiplied with ALL rows of the launch: the template parameter MODE = 16-row m-tiles per launch
+//     MODE 1: <= 16 rows; a cluster owns 8 rows of its head (half an m-tile), a CTA attends 2 rows
+//     MODE 2: <= 32 rows; a cluster owns one m-tile (16 rows), a CTA attends 4 rows
+//     MODE 4: <= 64 rows; a cluster owns two m-tiles (32 rows), a CTA attends 8 rows; phases B / C / head run the 64
+//             rows as two 32-row groups over the same resident weight chunks (the LayerNorm'd A operand of 32 rows
+//             is what fits next to the ring)
+// so that 32 (64) sequences cost one pass over the 773 MB of weights per step, not two (four).
 // Reference path replaced: GPT2InferenceModel.forward cached branch (unified_voice.py:212-229) + HF GPT2Block.
 #include <cstring>
 #include <cstdio>
@@ -23,27 +31,52 @@ constexpr int kU4PerChunk = kChunkBytes / 16;
 
 constexpr int kDecThreads = kConsumerThreads;     // 8 warps; there is no dedicated producer warp in this kernel
 
+template <int MODE>
+struct DecCfg {
+  static_assert(MODE == 1 || MODE == 2 || MODE == 4, "16, 32 or 64 rows");
+  static constexpr bool kHalf = MODE == 1;
+  static constexpr int kMtA = MODE == 4 ? 2 : 1;          // m-tiles a cluster multiplies in phase A
+  static constexpr int kRowsA = kHalf ? 8 : 16 * kMtA;    // rows of its head a cluster owns in phase A
+  static constexpr int kLnRowsA = 16 * kMtA;              // rows it normalises for that (whole m-tiles)
+  static constexpr int kAttnRows = kRowsA / kClusterSize; // attention rows per CTA: 2, 4, 8
+  static constexpr int kWarpsPerRow = kNW / kAttnRows;    // 4, 2, 1
+  static constexpr int kMtB = MODE == 1 ? 1 : 2;          // m-tiles per row group in phases B, C and the head
+  static constexpr int kGroups = MODE == 4 ? 2 : 1;       // row groups of 16 * kMtB rows
+  static constexpr int kMtSmem = kMtB;                    // m-tiles of the shared-memory A operand
+};
+
+// Shared-memory reduction buffer (Smem::red, 33 KiB) of these kernels, in floats:
+//   [0, 6144)      cross-warp split-K reduction of one m-tile (<= 6 tiles x 8 warps x 512 B); LayerNorm gains staged at
+//                  0 (ln_1, head) or 4096 (ln_2: above the 16 KiB its 4-tile reduction uses, so two row groups share them)
+//   [4096, 6144)   mlp.c_proj: K-partials received from the cluster's CTAs, [group][m-tile][source rank][64 pairs] float2
+//   [6144, 6784)   per-step row facts of this CTA (rinfo)
+//   [7168, 8192)   attention context of the cluster's head, <= 2 m-tiles x 64 dims bf16 in mma A-fragment order
+constexpr int kStageOffLn2 = 4096;
+constexpr int kXredOffsetFloats = 4096;
+constexpr int kRinfoOffsetFloats = 6144;
+constexpr int kCtxOffsetFloats = 7168;
+
 // ---- hardware cluster barrier (all 256 threads of the 4 CTAs; ~0.2 us).  release/acquire at cluster scope: global
 // and distributed-shared writes made before it are visible to the cluster's threads after it. -----------------------
 __device__ __forceinline__ void cluster_barrier() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
-// ---- weight feed: thread 0 of the CTA keeps the bulk-copy ring full --------------------------------------------------
+// ---- weight feed: warp 0 of the CTA keeps the bulk-copy ring full --------------------------------------------------
 // The chunk sequence of the whole launch is fixed (per layer: 6 c_attn, 2 split-K c_proj, 4 c_fc, 4 mlp.c_proj chunks;
-// then this CTA's mel-head chunks), so instead of a producer warp waiting on "slot empty" barriers, every stage that has
-// finished reading k ring slots (after a CTA barrier) lets thread 0 issue the next k chunks of the sequence into exactly
-// those slots.  The ring is therefore always n_slots chunks (more than half a layer) ahead of the consumers, across
-// grid barriers, steps and the sampler.
+// then this CTA's mel-head chunks, once per row group), so instead of a producer warp waiting on "slot empty" barriers,
+// every stage that has finished reading k ring slots (after a CTA barrier) lets warp 0 issue the next k chunks of the
+// sequence into exactly those slots.  The ring is therefore always n_slots chunks (half a layer or more) ahead of the
+// consumers, across grid barriers, steps and the sampler.
 struct Feed {
   uint32_t issued;           // chunks issued so far (uniform across the feed warp)
   uint32_t per_step, total;  // chunks per model pass / in the whole launch
   uint64_t pol;
 };
 
-__device__ __forceinline__ void feed_init(const Params& P, Feed& f, int hcnt) {
+__device__ __forceinline__ void feed_init(const Params& P, Feed& f, int hcnt, int groups) {
   f.issued = 0;
-  f.per_step = 16u * (uint32_t)P.n_layers + (uint32_t)hcnt;
+  f.per_step = 16u * (uint32_t)P.n_layers + (uint32_t)(groups * hcnt);
   f.total = f.per_step * (uint32_t)(P.n_steps - (P.skip_last_model ? 1 : 0));
   f.pol = make_evict_first_policy();
 }
@@ -68,7 +101,7 @@ __device__ __forceinline__ void feed(const Params& P, Ctrl* c, uint8_t* ring, Fe
       else if (i < 12) src = L + kOffFc + (size_t)(blockIdx.x * 4 + (i - 8)) * kU4PerChunk;
       else src = L + kOffProj2 + (size_t)(((blockIdx.x & ~3) + (i - 12)) * 4 + rank) * kU4PerChunk;   // tile 4c+i, K quarter = rank
     } else {
-      src = P.w_head + (size_t)(ht0 + (int)(r - 16u * (uint32_t)P.n_layers)) * kU4PerChunk;
+      src = P.w_head + (size_t)(ht0 + (int)((r - 16u * (uint32_t)P.n_layers) % (uint32_t)hcnt)) * kU4PerChunk;
     }
     mbar_arrive_expect_tx(&c->full[slot], kChunkBytes);
     bulk_g2s(ring + (size_t)slot * kChunkBytes, src, kChunkBytes, &c->full[slot], f.pol);
@@ -86,33 +119,30 @@ struct Feeder {
   int pending;               // ring slots read to the end since the last refill (uniform across the CTA's threads)
 };
 
-// ---- per-step row facts of this CTA, kept in shared memory (upper part of the reduction buffer) ----------------
+// ---- per-step row facts of this CTA, kept in shared memory ---------------------------------------------------------
 // Positions and page tables do not change inside a step, so the dependent global loads
 // (row_pos -> utterance -> prompt length -> page table -> page) are done once per step, not once per layer.
-//   [0..15] page of every row's new position (-1: inactive row)   [16..31] its slot in the page
-//   [32+j] kv length of attention row j (j < 2, 0: inactive)      [34+j] prompt length of its utterance
-//   [64 + 64j + i] prefix page table (i < 32) / private page table (i >= 32) of attention row j
-constexpr int kRinfoOffsetFloats = 7168;     // above the 24 KiB the 6-tile split-K reduction uses
+//   [i]      page of the new position of row tile_row0 + i (i < 32; -1: inactive row)   [32 + i] its slot in the page
+//   [64 + j] kv length of attention row j (j < 8, 0: inactive)      [72 + j] prompt length of its utterance
+//   [80 + 64 j + i] prefix page table (i < 32) / private page table (i >= 32) of attention row j
 __device__ __forceinline__ int* rinfo_ptr(const Smem& sm) { return reinterpret_cast<int*>(sm.red + kRinfoOffsetFloats); }
-// attention context of this cluster's head, 16 rows x 64 dims bf16 in mma A-fragment order (2 KiB): every CTA of the
-// cluster holds a full copy, written through distributed shared memory by the CTA that merged the row
-constexpr int kCtxOffsetFloats = 7680;
+// attention context of this cluster's head in mma A-fragment order (2 KiB per m-tile): every CTA of the cluster holds a
+// full copy, written through distributed shared memory by the CTA that merged the row
 __device__ __forceinline__ uint4* ctx_smem(const Smem& sm) { return reinterpret_cast<uint4*>(sm.red + kCtxOffsetFloats); }
 
-// Called by warps 4..7 only (threads 128..255), which are idle while warps 0..3 normalise: the dependent loads overlap
-// the LayerNorm instead of preceding it.  Ends with a named barrier over those 128 threads; everyone else sees the
-// facts after the cluster barrier that follows the LayerNorm.
-__device__ void build_rinfo(const Params& P, int rbase, const Smem& sm) {
+// Called by `nthr` (>= 72) threads (index t); the caller synchronises them afterwards.
+template <int MODE>
+__device__ __forceinline__ void build_rinfo(const Params& P, int tile_row0, int attn_row0, const Smem& sm, int t, int nthr) {
+  using C = DecCfg<MODE>;
   int* ri = rinfo_ptr(sm);
-  const int tid = threadIdx.x - 128;
-  {
-    const int j = tid >> 6, i = tid & 63, row = rbase + j;
+  for (int idx = t; idx < C::kAttnRows * 64; idx += nthr) {
+    const int j = idx >> 6, i = idx & 63, row = attn_row0 + j;
     int v = 0;
     if (row < P.n_rows) v = (i < 32) ? P.prefix_pt[P.row_utt[row] * kMaxPagesPerSeg + i] : P.priv_pt[row * kMaxPagesPerSeg + (i - 32)];
-    ri[64 + 64 * j + i] = v;
+    ri[80 + idx] = v;
   }
-  if (tid < 16) {
-    const int row = tid;
+  if (t < 16 * C::kMtA) {
+    const int row = tile_row0 + t;
     const int pos = (row < P.n_rows) ? ld_cg_i(P.row_pos + row) : -1;
     int page = -1, slot = 0;
     if (pos >= 0) {
@@ -120,84 +150,98 @@ __device__ void build_rinfo(const Params& P, int rbase, const Smem& sm) {
       page = P.priv_pt[row * kMaxPagesPerSeg + (pp >> 5)];
       slot = pp & 31;
     }
-    ri[row] = page;
-    ri[16 + row] = slot;
-  } else if (tid >= 32 && tid < 34) {
-    const int j = tid - 32, row = rbase + j;
+    ri[t] = page;
+    ri[32 + t] = slot;
+  } else if (t >= 64 && t < 64 + C::kAttnRows) {
+    const int j = t - 64, row = attn_row0 + j;
     const int pos = (row < P.n_rows) ? ld_cg_i(P.row_pos + row) : -1;
-    ri[32 + j] = pos + 1;
-    ri[34 + j] = (row < P.n_rows) ? P.utt_plen[P.row_utt[row]] : 0;
+    ri[64 + j] = pos + 1;
+    ri[72 + j] = (row < P.n_rows) ? P.utt_plen[P.row_utt[row]] : 0;
   }
-  asm volatile("bar.sync 2, 128;" ::: "memory");
 }
 
-// ---- cluster-cooperative LayerNorm: CTA rank r normalises rows 4r..4r+3 (warps 0..3, one row each) and writes
-// the bf16 rows into the A-operand buffer of all 4 CTAs of the cluster through distributed shared memory, so the
-// 16 rows are read from L2 once per cluster instead of once per CTA.  Warps 4..7 meanwhile pull the NEXT layer's
-// K/V pages of this CTA's attention rows into L2 (bulk prefetch), so the attention phase is not an HBM stall.
-// The caller follows with cluster_barrier().
+// Pull the NEXT layer's K/V pages of this CTA's attention rows and its small fp32 parameters into L2 (bulk prefetch), so
+// the attention phase and the LayerNorm / bias loads are not HBM stalls.  Called by `nthr` threads (index t).
+template <int MODE>
+__device__ __forceinline__ void prefetch_next(const Params& P, const Smem& sm, int head, int pf_layer, int t, int nthr) {
+  using C = DecCfg<MODE>;
+  if (pf_layer < 0 || pf_layer > P.n_layers) return;
+  // the small fp32 parameters (LN gains/biases, GEMM biases: one contiguous block per layer, tts_ar.cu) are
+  // read once per step and do not survive 1.3 GB of streaming in L2: pull the next block in, 1/128 per CTA
+  if (t == 0) {
+    if (pf_layer < P.n_layers) {
+      constexpr int kPer = ((4 * kD + kD3 + kD + kD4 + kD) * 4 / kDecCtas + 15) / 16 * 16;   // 416 B
+      bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(layer_f(P, pf_layer)) + (size_t)blockIdx.x * kPer, kPer);
+    } else {
+      const int per = ((4 * kD + P.v_stride) * 4 / kDecCtas + 15) / 16 * 16;
+      bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(P.lnf_g) + (size_t)blockIdx.x * per, per);
+    }
+  }
+  if (pf_layer >= P.n_layers) return;
+  const int* ri = rinfo_ptr(sm);
+  const size_t page_stride = (size_t)2 * kH * kPage * kHD;
+  for (int idx = t; idx < C::kAttnRows * 64; idx += nthr) {
+    const int j = idx >> 6, i = idx & 63, pg = i >> 1, kv = i & 1;
+    const int len = ri[64 + j], plen = ri[72 + j];
+    if (len <= 0) continue;
+    const int* pt = ri + 80 + 64 * j;
+    const __nv_bfloat16* base = P.kv + kv_row_offset(pf_layer, P.n_pages, 0, kv, head, 0);
+    if (pg * kPage < plen) bulk_prefetch_l2(base + (size_t)pt[pg] * page_stride, kPage * kHD * 2);
+    if (pg * kPage < len - plen) bulk_prefetch_l2(base + (size_t)pt[32 + pg] * page_stride, kPage * kHD * 2);
+  }
+}
+
+// ---- cluster-cooperative LayerNorm: CTA rank r normalises rows rbase + npc r .. + npc - 1 (one warp per row) and
+// writes the bf16 rows into rows npc r .. of the A-operand buffer of all 4 CTAs of the cluster through distributed shared
+// memory, so the rows are read from L2 once per cluster instead of once per CTA.  The caller follows with cluster_barrier().
 // `gb` = the staged (gain, bias) vectors: one pair, or two for the head (ln_f then final_norm, `dbl`); the head is the
 // same call site as ln_1 on purpose -- code that runs once per step is fetched cold, code shared with the layers is not.
-__device__ __forceinline__ void ln_cluster(const Params& P, const Instr& ins, const Smem& sm, const float* src, const float* gb, bool dbl,
-                                           int rank, int head, int pf_layer, int rinfo_rbase) {
+// `fixed`: the source is the fixed-point accumulator y (ln_2) instead of x.
+__device__ __forceinline__ void ln_cluster(const Params& P, const Smem& sm, bool fixed, const float* gb, bool dbl, int rank, int rbase,
+                                           int npc) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  if (w < 4) {
-    const int r = 4 * rank + w;
-    const bool ok = r < ins.nrows;
-    const int lrow = ins.row0 + (ok ? r : 0);
-    float4 v[8];
-    ln_load_row(P, ins, src, lrow, lane, v);
-    prof_mark(P, sm.ctrl, 21);
-    const int npass = dbl ? 2 : 1;
-#pragma unroll 1
-    for (int p = 0; p < npass; ++p) ln_normalise(v, gb + 2 * p * kD, gb + (2 * p + 1) * kD, lane);
-    prof_mark(P, sm.ctrl, 22);
-    if (dbl && blockIdx.x < kClusterSize && ok) {      // final_norm(ln_f(x)): the latent of this step
-      float* lp = P.cur_latent + (size_t)lrow * kD;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) *reinterpret_cast<float4*>(lp + 128 * j + 4 * lane) = v[j];
-    }
-    uint8_t* dst = sm.a_rm + (size_t)r * kARowBytes;
+  if (w >= npc) return;
+  const int r = npc * rank + w;
+  const int grow = rbase + r;
+  const bool ok = grow < P.n_rows;
+  const int lrow = ok ? grow : 0;
+  float4 v[8];
+  if (fixed) {
+    const long long* yp = P.y + (size_t)lrow * kD;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const uint2 pk = ok ? make_uint2(pack_bf16x2(v[j].x, v[j].y), pack_bf16x2(v[j].z, v[j].w)) : make_uint2(0u, 0u);
-#pragma unroll
-      for (int d = 0; d < kClusterSize; ++d) st_cluster_u2(dst + (128 * j + 4 * lane) * 2, d, pk);
+      const longlong2 a = ld_cg_ll2(yp + 128 * j + 4 * lane), b = ld_cg_ll2(yp + 128 * j + 4 * lane + 2);
+      v[j] = make_float4(from_fixed(a.x), from_fixed(a.y), from_fixed(b.x), from_fixed(b.y));
     }
-    prof_mark(P, sm.ctrl, 23);
   } else {
-    if (rinfo_rbase >= 0) build_rinfo(P, rinfo_rbase, sm);
-    if (pf_layer >= 0 && pf_layer <= P.n_layers) {
-    const int t = threadIdx.x - 128;                 // 0..127
-    // the small fp32 parameters (LN gains/biases, GEMM biases: one contiguous block per layer, tts_ar.cu) are
-    // read once per step and do not survive 1.3 GB of streaming in L2: pull the next block in, 1/128 per CTA
-    if (t == 0) {
-      if (pf_layer < P.n_layers) {
-        constexpr int kPer = ((4 * kD + kD3 + kD + kD4 + kD) * 4 / kDecCtas + 15) / 16 * 16;   // 416 B
-        bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(layer_f(P, pf_layer)) + (size_t)blockIdx.x * kPer, kPer);
-      } else {
-        const int per = ((4 * kD + P.v_stride) * 4 / kDecCtas + 15) / 16 * 16;
-        bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(P.lnf_g) + (size_t)blockIdx.x * per, per);
-      }
-    }
-    const int* ri = rinfo_ptr(sm);
-    const int j = t >> 6, i = t & 63, pg = i >> 1, kv = i & 1;
-    const int len = ri[32 + j], plen = ri[34 + j];
-    if (pf_layer < P.n_layers && len > 0) {
-      const int* pt = ri + 64 + 64 * j;
-      const __nv_bfloat16* base = P.kv + kv_row_offset(pf_layer, P.n_pages, 0, kv, head, 0);
-      const size_t page_stride = (size_t)2 * kH * kPage * kHD;
-      if (pg * kPage < plen) bulk_prefetch_l2(base + (size_t)pt[pg] * page_stride, kPage * kHD * 2);
-      if (pg * kPage < len - plen) bulk_prefetch_l2(base + (size_t)pt[32 + pg] * page_stride, kPage * kHD * 2);
-    }
-    }
+    const float* xp = P.x + (size_t)lrow * kD;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = ld_cg_f4(xp + 128 * j + 4 * lane);
   }
+  prof_mark(P, sm.ctrl, 21);
+  const int npass = dbl ? 2 : 1;
+#pragma unroll 1
+  for (int p = 0; p < npass; ++p) ln_normalise(v, gb + 2 * p * kD, gb + (2 * p + 1) * kD, lane);
+  prof_mark(P, sm.ctrl, 22);
+  if (dbl && blockIdx.x < kClusterSize && ok) {      // final_norm(ln_f(x)): the latent of this step
+    float* lp = P.cur_latent + (size_t)lrow * kD;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) *reinterpret_cast<float4*>(lp + 128 * j + 4 * lane) = v[j];
+  }
+  uint8_t* dst = sm.a_rm + (size_t)r * kARowBytes;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const uint2 pk = ok ? make_uint2(pack_bf16x2(v[j].x, v[j].y), pack_bf16x2(v[j].z, v[j].w)) : make_uint2(0u, 0u);
+#pragma unroll
+    for (int d = 0; d < kClusterSize; ++d) st_cluster_u2(dst + (128 * j + 4 * lane) * 2, d, pk);
+  }
+  prof_mark(P, sm.ctrl, 23);
 }
 
-// ---- attention of head `head` for rows rbase, rbase+1 ------------------------------------------------------------
-// Warp w: row rbase + (w >> 2), quarter (w & 3) of the row's 16-position granules (a granule never straddles a
-// page).  K/V granules are double-buffered in registers so the next granule's 128-bit loads are in flight while
-// earlier ones are reduced; the four partial (max, sum, acc) states of a row are merged in shared memory.
+// ---- attention of head `head` for this CTA's rows --------------------------------------------------------------------
+// Warp w: attention row w / kWarpsPerRow, share (w % kWarpsPerRow) of the row's 16-position granules (a granule never
+// straddles a page).  K/V granules are triple-buffered in registers so the next granules' 128-bit loads are in flight
+// while earlier ones are reduced; the partial (max, sum, acc) states of a row are merged in shared memory.
 struct Gran {
   uint4 k[4], v[4];
   int cnt;
@@ -272,24 +316,54 @@ __device__ __forceinline__ void gran_reduce(const Gran& G, const float (&qv)[8],
   m = m_new;
 }
 
-__device__ void attn_local(const Params& P, int layer, int head, int rbase, const Smem& sm) {
+// A row's positions are ALWAYS cut into 4 quarter ranges of 16-position granules, each reduced to its own partial
+// (max, sum, acc) and merged in quarter order, whatever the number of warps per row: warp w streams the quarters
+// (w % WPR) * 4 / WPR .. of row w / WPR back to back (the loads run on across quarter boundaries), so the result of a
+// row is bit-identical in every MODE.
+// ctx_row0: row index (inside the cluster's m-tiles) of attention row 0 of this CTA
+template <int MODE>
+__device__ void attn_local(const Params& P, int layer, int head, int attn_row0, int ctx_row0, const Smem& sm) {
+  using C = DecCfg<MODE>;
+  constexpr int WPR = C::kWarpsPerRow;
+  constexpr int QPW = 4 / WPR;                        // quarters per warp: 1, 2, 4
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int rg = lane >> 3, dc = lane & 7;
   const int* ri = rinfo_ptr(sm);
-  float* part = sm.red;                               // [8 warps][kPartStride]
+  float* part = sm.red;                               // [attention row][quarter][kPartStride]
   {
-    const int j = w >> 2, s = w & 3, row = rbase + j;
-    const int len = ri[32 + j], plen = ri[34 + j];
+    const int j = w / WPR, s = w % WPR, row = attn_row0 + j;
+    const int len = ri[64 + j], plen = ri[72 + j];
     float m = -INFINITY, l = 0.f, acc[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    int q = s * QPW;                                  // quarter being accumulated
+    auto flush = [&]() {                              // finish quarter q: reduce over the 4 row groups, park the partial, reset
+      float ll = l;
+      ll += __shfl_xor_sync(0xffffffffu, ll, 8);
+      ll += __shfl_xor_sync(0xffffffffu, ll, 16);
+      float* pp = part + (j * 4 + q) * kPartStride;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 8);
+        acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 16);
+      }
+      if (rg == 0) {
+        *reinterpret_cast<float4*>(pp + 8 + dc * 8) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+        *reinterpret_cast<float4*>(pp + 8 + dc * 8 + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+      }
+      if (lane == 0) { pp[0] = m; pp[1] = ll; }
+      m = -INFINITY; l = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+      ++q;
+    };
     if (len > 0) {
       const int Gp = (plen + 15) >> 4, Gt = Gp + ((len - plen + 15) >> 4);
-      const int g0 = (s * Gt) >> 2, g1 = ((s + 1) * Gt) >> 2;
+      const int g0 = (s * QPW * Gt) >> 2, g1 = ((s + 1) * QPW * Gt) >> 2;
       if (g1 > g0) {
-        const int* pt = ri + 64 + 64 * j;
+        const int* pt = ri + 80 + 64 * j;
         const __nv_bfloat16* kvb = P.kv + kv_row_offset(layer, P.n_pages, 0, 0, head, 0) + dc * 8;
-        Gran A, B, C;                                  // three granules in flight per warp (12 KiB)
+        Gran A, B, Cg;                                 // three granules in flight per warp (12 KiB)
         gran_load(A, kvb, pt, g0, Gp, plen, len, rg);
         if (g0 + 1 < g1) gran_load(B, kvb, pt, g0 + 1, Gp, plen, len, rg);
         float qv[8];
@@ -299,39 +373,30 @@ __device__ void attn_local(const Params& P, int layer, int head, int rbase, cons
           qv[0] = a.x * kLog2e; qv[1] = a.y * kLog2e; qv[2] = a.z * kLog2e; qv[3] = a.w * kLog2e;
           qv[4] = b.x * kLog2e; qv[5] = b.y * kLog2e; qv[6] = b.z * kLog2e; qv[7] = b.w * kLog2e;
         }
+        int qend = ((q + 1) * Gt) >> 2;               // first granule of the next quarter
         for (int g = g0; g < g1; g += 3) {
-          if (g + 2 < g1) gran_load(C, kvb, pt, g + 2, Gp, plen, len, rg);
+          if (g + 2 < g1) gran_load(Cg, kvb, pt, g + 2, Gp, plen, len, rg);
+          if (QPW > 1) while (g >= qend) { flush(); qend = ((q + 1) * Gt) >> 2; }
           gran_reduce(A, qv, rg, m, l, acc);
           if (g + 1 < g1) {
             if (g + 3 < g1) gran_load(A, kvb, pt, g + 3, Gp, plen, len, rg);
+            if (QPW > 1) while (g + 1 >= qend) { flush(); qend = ((q + 1) * Gt) >> 2; }
             gran_reduce(B, qv, rg, m, l, acc);
           }
           if (g + 2 < g1) {
             if (g + 4 < g1) gran_load(B, kvb, pt, g + 4, Gp, plen, len, rg);
-            gran_reduce(C, qv, rg, m, l, acc);
+            if (QPW > 1) while (g + 2 >= qend) { flush(); qend = ((q + 1) * Gt) >> 2; }
+            gran_reduce(Cg, qv, rg, m, l, acc);
           }
-        }
-        l += __shfl_xor_sync(0xffffffffu, l, 8);
-        l += __shfl_xor_sync(0xffffffffu, l, 16);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 8);
-          acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 16);
         }
       }
     }
     prof_mark(P, sm.ctrl, 12);
-    float* pp = part + w * kPartStride;
-    if (rg == 0) {
-      *reinterpret_cast<float4*>(pp + 8 + dc * 8) = make_float4(acc[0], acc[1], acc[2], acc[3]);
-      *reinterpret_cast<float4*>(pp + 8 + dc * 8 + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
-    }
-    if (lane == 0) { pp[0] = m; pp[1] = l; }
+    while (q < (s + 1) * QPW) flush();                 // the last quarter, and quarters without a granule (empty partials)
   }
   consumer_sync();
-  if (w < 2) {
-    const int row = rbase + w;
-    const int len = ri[32 + w];
+  if (w < C::kAttnRows) {
+    const int len = ri[64 + w];
     float o0 = 0.f, o1 = 0.f;
     if (len > 0) {
       const float* pb = part + (4 * w) * kPartStride;
@@ -352,7 +417,7 @@ __device__ void attn_local(const Params& P, int layer, int head, int rbase, cons
       o1 *= inv;
     }
     // the split-K c_proj of all 4 CTAs reads this row: push the pair into everyone's copy
-    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(ctx_smem(sm)) + afrag_elem_offset(row, 2 * lane, kHD);
+    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(ctx_smem(sm)) + afrag_elem_offset(ctx_row0 + w, 2 * lane, kHD);
     const uint32_t pk = pack_bf16x2(o0, o1);
 #pragma unroll
     for (int d = 0; d < kClusterSize; ++d) st_cluster_u32(dst, d, pk);
@@ -380,19 +445,24 @@ __device__ __forceinline__ void wait_chunks(Ctrl* c, const Pipe& pipe, int cnt) 
   }
 }
 
-// ---- 16-row GEMM over this CTA's next `cnt` (<= NT) streamed K=1024 chunks ------------------------------------------
+// ---- GEMM of MT 16-row m-tiles over this CTA's next `cnt` (<= NT) streamed K=1024 chunks ------------------------------
 // A = the LayerNorm'd rows staged in sm.a_rm; warp w owns k16-blocks 8w..8w+7 of every chunk (its A fragments
-// are loaded once), the 8 partial tiles are summed through shared memory in a fixed order (deterministic).
-// HALF: only rows [row_lo, row_lo + 8) are produced (c_attn: the other half belongs to the sibling cluster).
-// epi(row, col, v0, v1) receives the fp32 sums of columns col, col+1 (col = 8 * tile_of(i) + even offset).
-// `bias` (indexed by output column) is fetched before the mma loop for the (at most two) pairs a thread finishes.
-template <int NT, bool HALF, bool TAILSYNC, typename TileFn, typename Epi>
+// are loaded once), the 8 partial tiles are summed through shared memory in a fixed order (deterministic), one m-tile per
+// round.  HALF (MT == 1 only): only rows [row_lo, row_lo + 8) are produced (MODE 1 c_attn: the other half belongs to the
+// sibling cluster).  epi(row, col, v0, v1) receives the fp32 sums of columns col, col+1 (col = 8 * tile_of(i) + even
+// offset) of row `row` of the A operand (0 .. 16 MT - 1).  `bias` (indexed by output column) is fetched before the mma
+// loop for the (at most two) pairs a thread finishes.  `commit`: the chunks are done with (false: another row group of
+// the same stage re-reads them).
+template <int NT, int MT, bool HALF, bool TAILSYNC, typename TileFn, typename Epi>
 __device__ __forceinline__ void gemm16(const Params& P, const Smem& sm, Pipe& pipe, Feeder& fd, int cnt, int row_lo, const float* bias,
-                                       TileFn tile_of, Epi epi) {
+                                       bool commit, TileFn tile_of, Epi epi) {
+  static_assert(!HALF || MT == 1, "half tiles are a MODE 1 notion");
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   Ctrl* c = sm.ctrl;
   constexpr int kPerTile = HALF ? 32 : 64;
   constexpr int kMaxE = (NT * kPerTile + kConsumerThreads - 1) / kConsumerThreads;
+  constexpr int CH = 2;                             // two accumulator chains per (tile, m-tile) in EVERY mode: a row's fp32 summation
+                                                    // order does not depend on how many rows share the launch (bit-identical results)
   float2 bpre[kMaxE];
 #pragma unroll
   for (int k = 0; k < kMaxE; ++k) {
@@ -404,18 +474,25 @@ __device__ __forceinline__ void gemm16(const Params& P, const Smem& sm, Pipe& pi
       bpre[k] = *reinterpret_cast<const float2*>(bias + tile_of(t) * 8 + 2 * (ln & 3));
     }
   }
-  uint4 a[8];
+  uint4 a[MT][8];
   {
     const uint32_t base = smem_u32(sm.a_rm) + (uint32_t)(((lane & 7) + ((lane >> 3) & 1) * 8) * kARowBytes) +
                           (uint32_t)((lane >> 4) * 16) + (uint32_t)(w * 8 * 32);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) ldmatrix_x4(base + (uint32_t)(i * 32), a[i].x, a[i].y, a[i].z, a[i].w);
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        ldmatrix_x4(base + (uint32_t)(mt * 16 * kARowBytes) + (uint32_t)(i * 32), a[mt][i].x, a[mt][i].y, a[mt][i].z, a[mt][i].w);
   }
-  float acc[NT][2][4];
+  float acc[NT][MT][CH][4];
 #pragma unroll
   for (int t = 0; t < NT; ++t)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) acc[t][0][j] = acc[t][1][j] = 0.f;
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+      for (int ch = 0; ch < CH; ++ch)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[t][mt][ch][j] = 0.f;
   prof_mark(P, c, 5);
   wait_chunks(c, pipe, cnt);     // all chunks of the pass have normally landed long ago
   Pipe p2 = pipe;
@@ -427,88 +504,75 @@ __device__ __forceinline__ void gemm16(const Params& P, const Smem& sm, Pipe& pi
 #pragma unroll
       for (int s2 = 0; s2 < 4; ++s2) {
         const uint4 b = bsm[s2 * 32];
-        mma_bf16_16816(acc[t][s2 & 1], a[2 * s2], b.x, b.y);
-        mma_bf16_16816(acc[t][s2 & 1], a[2 * s2 + 1], b.z, b.w);
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt) {
+          mma_bf16_16816(acc[t][mt][s2 & (CH - 1)], a[mt][2 * s2], b.x, b.y);
+          mma_bf16_16816(acc[t][mt][s2 & (CH - 1)], a[mt][2 * s2 + 1], b.z, b.w);
+        }
       }
       p2.advance();
     }
-  pipe = p2;
+  if (commit) pipe = p2;
   prof_mark(P, c, 2);
   float4* red4 = reinterpret_cast<float4*>(sm.red);
-#pragma unroll
-  for (int t = 0; t < NT; ++t)
-    if (t < cnt)
-      red4[(w * NT + t) * 32 + lane] = make_float4(acc[t][0][0] + acc[t][1][0], acc[t][0][1] + acc[t][1][1],
-                                                   acc[t][0][2] + acc[t][1][2], acc[t][0][3] + acc[t][1][3]);
-  consumer_sync();
-  prof_mark(P, c, 4);
-  fd.pending += cnt;                     // every warp is done with the cnt ring slots; refilled at the next grid barrier
   const float2* red2 = reinterpret_cast<const float2*>(sm.red);
-  const int per_tile = kPerTile;
 #pragma unroll
-  for (int q = 0; q < kMaxE; ++q) {
-    const int e = threadIdx.x + q * kConsumerThreads;
-    if (e >= cnt * per_tile) break;
-    const int t = e / per_tile, rem = e - t * per_tile;
-    const int ln = HALF ? rem : (rem >> 1);
-    const int hh = HALF ? (row_lo >> 3) : (rem & 1);
-    float s0 = 0.f, s1 = 0.f;
+  for (int mt = 0; mt < MT; ++mt) {
 #pragma unroll
-    for (int k = 0; k < kNW; ++k) {
-      const float2 v = red2[((k * NT + t) * 32 + ln) * 2 + hh];
-      s0 += v.x;
-      s1 += v.y;
+    for (int t = 0; t < NT; ++t)
+      if (t < cnt)
+        red4[(w * NT + t) * 32 + lane] = make_float4(acc[t][mt][0][0] + acc[t][mt][1][0], acc[t][mt][0][1] + acc[t][mt][1][1],
+                                                     acc[t][mt][0][2] + acc[t][mt][1][2], acc[t][mt][0][3] + acc[t][mt][1][3]);
+    consumer_sync();
+    prof_mark(P, c, 4);
+#pragma unroll
+    for (int q = 0; q < kMaxE; ++q) {
+      const int e = threadIdx.x + q * kConsumerThreads;
+      if (e >= cnt * kPerTile) break;
+      const int t = e / kPerTile, rem = e - t * kPerTile;
+      const int ln = HALF ? rem : (rem >> 1);
+      const int hh = HALF ? (row_lo >> 3) : (rem & 1);
+      float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+      for (int k = 0; k < kNW; ++k) {
+        const float2 v = red2[((k * NT + t) * 32 + ln) * 2 + hh];
+        s0 += v.x;
+        s1 += v.y;
+      }
+      epi(16 * mt + (ln >> 2) + 8 * hh, tile_of(t) * 8 + 2 * (ln & 3), s0 + bpre[q].x, s1 + bpre[q].y);
     }
-    epi((ln >> 2) + 8 * hh, tile_of(t) * 8 + 2 * (ln & 3), s0 + bpre[q].x, s1 + bpre[q].y);
+    if (TAILSYNC || mt + 1 < MT) consumer_sync();   // else: the caller's next cluster / grid barrier protects the reduction buffer
   }
+  if (commit) fd.pending += cnt;         // every warp is done with the cnt ring slots; refilled at the next grid barrier
   prof_mark(P, c, 3);
-  if (TAILSYNC) consumer_sync();   // else: the caller's next cluster / grid barrier protects the reduction buffer
 }
 
 // ---- split-K attn.c_proj: y[rows, 256r .. 256r+256) += ctx[rows, 64h .. 64h+64) . W[64h .. 64h+64, 256r ..] ------
-// rows = [row_lo, row_lo + 8): the half of the 16-row M tile this cluster owns (the other half of the A fragments
-// is the sibling cluster's and is ignored).  Two 16 KiB chunks of 128 columns; warp w: n8-tiles 2w, 2w+1 of each.
-// Residual + bias ride on head 0's partial product: its CTAs fetch x and the bias at the start of phase A (x is final
-// since the grid barrier), so the loads are not on the path between the attention and the atomics.
-struct ProjAdd { float2 v[2][2]; };
-__device__ __forceinline__ void proj_preload(const Params& P, int layer, int head, int rank, int row_lo, ProjAdd& pa) {
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int row = row_lo + (lane >> 2);
-#pragma unroll
-  for (int ch = 0; ch < 2; ++ch)
-#pragma unroll
-    for (int tt = 0; tt < 2; ++tt) {
-      pa.v[ch][tt] = make_float2(0.f, 0.f);
-      if (head == 0 && row < P.n_rows) {
-        const int col = 256 * rank + 128 * ch + 16 * w + 2 * (lane & 3) + 8 * tt;
-        const float2 b = *reinterpret_cast<const float2*>(layer_f(P, layer) + kFOffBproj + col);
-        const float2 xo = ld_cg_f2(P.x + (size_t)row * kD + col);
-        pa.v[ch][tt] = make_float2(xo.x + b.x, xo.y + b.y);
-      }
-    }
-}
-
-__device__ void proj_splitk(const Params& P, int layer, int head, int rank, int row_lo, const Smem& sm, Pipe& pipe,
-                            const ProjAdd& pa) {
+// rows = the rows of its head this cluster owns (MODE 1: half of the single m-tile, the other half of the A fragments is
+// the sibling cluster's and is ignored).  Two 16 KiB chunks of 128 columns; warp w: n8-tiles 2w, 2w+1 of each.
+// The residual and the bias are already in y (left there by the previous stage), so all 16 heads do the same work.
+template <int MODE>
+__device__ void proj_splitk(const Params& P, int rank, int row_lo, int tile_row0, const Smem& sm, Pipe& pipe) {
+  using C = DecCfg<MODE>;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   Ctrl* c = sm.ctrl;
-  uint4 a[4];                                      // A fragments of the head's context: kb = 0..3 of the local copy
+  uint4 a[C::kMtA][4];                             // A fragments of the head's context: kb = 0..3 of the local copy
 #pragma unroll
-  for (int j = 0; j < 4; ++j) a[j] = ctx_smem(sm)[j * 32 + lane];
+  for (int mt = 0; mt < C::kMtA; ++mt)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) a[mt][j] = ctx_smem(sm)[(mt * 4 + j) * 32 + lane];
   const int g = lane >> 2, t = lane & 3;
-  const int hh = row_lo >> 3;                      // which half of the C fragment is ours: regs 2hh, 2hh+1
-  const int row = row_lo + g;
-  const bool row_ok = row < P.n_rows;
   wait_chunks(c, pipe, 2);
 #pragma unroll
   for (int ch = 0; ch < 2; ++ch) {
     const int col0 = 256 * rank + 128 * ch + 16 * w + 2 * t;       // tile tt adds 8
-    const float2 add[2] = {pa.v[ch][0], pa.v[ch][1]};
-    float acc[2][4];
+    float acc[C::kMtA][2][4];
 #pragma unroll
-    for (int tt = 0; tt < 2; ++tt)
+    for (int mt = 0; mt < C::kMtA; ++mt)
 #pragma unroll
-      for (int j = 0; j < 4; ++j) acc[tt][j] = 0.f;
+      for (int tt = 0; tt < 2; ++tt)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[mt][tt][j] = 0.f;
     {
       const uint4* bsm = reinterpret_cast<const uint4*>(sm.ring + (size_t)pipe.slot * kChunkBytes) + lane;
 #pragma unroll
@@ -516,52 +580,69 @@ __device__ void proj_splitk(const Params& P, int layer, int head, int rank, int 
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
           const uint4 b = bsm[(((2 * w + tt) * 2) + s) * 32];
-          mma_bf16_16816(acc[tt], a[2 * s], b.x, b.y);
-          mma_bf16_16816(acc[tt], a[2 * s + 1], b.z, b.w);
+#pragma unroll
+          for (int mt = 0; mt < C::kMtA; ++mt) {
+            mma_bf16_16816(acc[mt][tt], a[mt][2 * s], b.x, b.y);
+            mma_bf16_16816(acc[mt][tt], a[mt][2 * s + 1], b.z, b.w);
+          }
         }
       }
     }
     pipe.advance();
-    if (row_ok) {
 #pragma unroll
-      for (int tt = 0; tt < 2; ++tt)
-      {
-        long long* yp = P.y + (size_t)row * kD + col0 + 8 * tt;
-        red_add_s64(yp, to_fixed((hh ? acc[tt][2] : acc[tt][0]) + add[tt].x));
-        red_add_s64(yp + 1, to_fixed((hh ? acc[tt][3] : acc[tt][1]) + add[tt].y));
+    for (int mt = 0; mt < C::kMtA; ++mt)
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        if (C::kHalf && hh != (row_lo >> 3)) continue;             // the other half of the tile is the sibling cluster's
+        const int row = tile_row0 + 16 * mt + 8 * hh + g;
+        if (row >= P.n_rows) continue;
+#pragma unroll
+        for (int tt = 0; tt < 2; ++tt) {
+          long long* yp = P.y + (size_t)row * kD + col0 + 8 * tt;
+          red_add_s64(yp, to_fixed(acc[mt][tt][2 * hh]));
+          red_add_s64(yp + 1, to_fixed(acc[mt][tt][2 * hh + 1]));
+        }
       }
-    }
   }
 }
 
-// ---- mlp.c_proj: x = y + h . W + bias ; y handed back zeroed ------------------------------------------------------------
+// ---- mlp.c_proj of row group `grp`: x = y + h . W + bias ; y = x + next layer's attn.c_proj bias -----------------------
 // A cluster owns 4 n8-tiles (32 output columns); CTA rank r multiplies the K range [1024r, 1024r+1024) of h with the 4
-// tiles (4 streamed chunks), so it reads only its quarter of h (32 KiB of bf16 A fragments from L2 instead of 128 KiB:
-// the SM's ~55 GB/s L2 read port is what this stage waits for).  The four K-partials of a tile are sent to the tile's
-// owner (rank t owns tile t) through distributed shared memory and summed there in rank order (deterministic).
-constexpr int kXredOffsetFloats = 6144;     // [4 source ranks][64 pairs] float2, above the 16 KiB in-CTA reduction
-__device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pipe, Feeder& fd, int rank) {
+// tiles (4 streamed chunks), so it reads only its quarter of h (32 KiB of bf16 A fragments per m-tile from L2 instead of
+// 128 KiB: the SM's ~55 GB/s L2 read port is what this stage waits for).  The four K-partials of a tile are sent to the
+// tile's owner (rank t owns tile t) through distributed shared memory and summed there in rank order (deterministic).
+template <int MODE>
+__device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pipe, Feeder& fd, int rank, int grp, bool commit) {
+  using C = DecCfg<MODE>;
+  constexpr int MT = C::kMtB;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   Ctrl* c = sm.ctrl;
-  const uint4* a_gl = reinterpret_cast<const uint4*>(P.hbuf) + (size_t)(rank * kKbPerChunk + w * 8) * 32 + lane;   // m-tile 0
-  uint4 a[8];
+  uint4 a[MT][8];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) a[i] = ld_cg_u4(a_gl + (size_t)i * 32);
-  // epilogue operands of the threads that own an output pair of tile `rank` (64 pairs: 16 rows x 4 column pairs)
-  const int col = ((blockIdx.x & ~3) + rank) * 8 + 2 * ((threadIdx.x >> 1) & 3);
-  const int erow = (threadIdx.x >> 3) + 8 * (threadIdx.x & 1);
-  const bool owner = threadIdx.x < 64 && erow < P.n_rows;
+  for (int mt = 0; mt < MT; ++mt) {
+    const uint4* a_gl = reinterpret_cast<const uint4*>(P.hbuf) + ((size_t)(grp * MT + mt) * (kD4 >> 4) + rank * kKbPerChunk + w * 8) * 32 + lane;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a[mt][i] = ld_cg_u4(a_gl + (size_t)i * 32);
+  }
+  // epilogue operands of the threads that own an output pair of tile `rank` (64 pairs per m-tile: 16 rows x 4 column pairs)
+  const int emt = threadIdx.x >> 6, erem = threadIdx.x & 63;
+  const int col = ((blockIdx.x & ~3) + rank) * 8 + 2 * ((erem >> 1) & 3);
+  const int erow = 16 * (grp * MT + emt) + (erem >> 3) + 8 * (erem & 1);
+  const bool owner = emt < MT && erow < P.n_rows;
   longlong2 old = make_longlong2(0ll, 0ll);
-  float2 bias = make_float2(0.f, 0.f);
+  float2 bias = make_float2(0.f, 0.f), nbias = make_float2(0.f, 0.f);
   if (owner) {
     old = ld_cg_ll2(P.y + (size_t)erow * kD + col);
     bias = *reinterpret_cast<const float2*>(layer_f(P, layer) + kFOffBproj2 + col);
+    if (layer + 1 < P.n_layers) nbias = *reinterpret_cast<const float2*>(layer_f(P, layer + 1) + kFOffBproj + col);
   }
-  float acc[4][2][4];
+  float acc[4][MT][2][4];
 #pragma unroll
   for (int t = 0; t < 4; ++t)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) acc[t][0][j] = acc[t][1][j] = 0.f;
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[t][mt][0][j] = acc[t][mt][1][j] = 0.f;
   wait_chunks(c, pipe, 4);
   Pipe p2 = pipe;
 #pragma unroll
@@ -570,20 +651,25 @@ __device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pi
 #pragma unroll
     for (int s2 = 0; s2 < 4; ++s2) {
       const uint4 b = bsm[s2 * 32];
-      mma_bf16_16816(acc[t][s2 & 1], a[2 * s2], b.x, b.y);
-      mma_bf16_16816(acc[t][s2 & 1], a[2 * s2 + 1], b.z, b.w);
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt) {
+        mma_bf16_16816(acc[t][mt][s2 & 1], a[mt][2 * s2], b.x, b.y);
+        mma_bf16_16816(acc[t][mt][s2 & 1], a[mt][2 * s2 + 1], b.z, b.w);
+      }
     }
     p2.advance();
   }
-  pipe = p2;
+  if (commit) pipe = p2;
   float4* red4 = reinterpret_cast<float4*>(sm.red);
+  float2* xred = reinterpret_cast<float2*>(sm.red + kXredOffsetFloats) + (size_t)grp * MT * kClusterSize * 64;
 #pragma unroll
-  for (int t = 0; t < 4; ++t)
-    red4[(w * 4 + t) * 32 + lane] = make_float4(acc[t][0][0] + acc[t][1][0], acc[t][0][1] + acc[t][1][1],
-                                                acc[t][0][2] + acc[t][1][2], acc[t][0][3] + acc[t][1][3]);
-  consumer_sync();
-  fd.pending += 4;
-  {
+  for (int mt = 0; mt < MT; ++mt) {
+    if (mt) consumer_sync();             // the previous round's sums have been read
+#pragma unroll
+    for (int t = 0; t < 4; ++t)
+      red4[(w * 4 + t) * 32 + lane] = make_float4(acc[t][mt][0][0] + acc[t][mt][1][0], acc[t][mt][0][1] + acc[t][mt][1][1],
+                                                  acc[t][mt][0][2] + acc[t][mt][1][2], acc[t][mt][0][3] + acc[t][mt][1][3]);
+    consumer_sync();
     // this CTA's K-partial of pair (tile t, ln, hh) -> owner CTA t
     const float2* red2 = reinterpret_cast<const float2*>(sm.red);
     const int t = threadIdx.x >> 6, rem = threadIdx.x & 63, ln = rem >> 1, hh = rem & 1;
@@ -594,35 +680,37 @@ __device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pi
       s0 += v.x;
       s1 += v.y;
     }
-    float2* xred = reinterpret_cast<float2*>(sm.red + kXredOffsetFloats);
-    st_cluster_u2(xred + rank * 64 + rem, (uint32_t)t, make_uint2(__float_as_uint(s0), __float_as_uint(s1)));
+    st_cluster_u2(xred + (mt * kClusterSize + rank) * 64 + rem, (uint32_t)t, make_uint2(__float_as_uint(s0), __float_as_uint(s1)));
   }
+  if (commit) fd.pending += 4;
   cluster_barrier();
   if (owner) {
-    const float2* xred = reinterpret_cast<const float2*>(sm.red + kXredOffsetFloats);
     float s0 = 0.f, s1 = 0.f;
 #pragma unroll
     for (int r = 0; r < kClusterSize; ++r) {
-      const float2 v = xred[r * 64 + threadIdx.x];
+      const float2 v = xred[(emt * kClusterSize + r) * 64 + erem];
       s0 += v.x;
       s1 += v.y;
     }
-    *reinterpret_cast<float2*>(P.x + (size_t)erow * kD + col) =
-        make_float2(from_fixed(old.x) + s0 + bias.x, from_fixed(old.y) + s1 + bias.y);
-    *reinterpret_cast<longlong2*>(P.y + (size_t)erow * kD + col) = make_longlong2(0ll, 0ll);
+    const float x0 = from_fixed(old.x) + s0 + bias.x, x1 = from_fixed(old.y) + s1 + bias.y;
+    *reinterpret_cast<float2*>(P.x + (size_t)erow * kD + col) = make_float2(x0, x1);
+    // the next layer's attention block accumulates onto residual + attn.c_proj bias
+    *reinterpret_cast<longlong2*>(P.y + (size_t)erow * kD + col) = make_longlong2(to_fixed(x0 + nbias.x), to_fixed(x1 + nbias.y));
   }
 }
 
 // ---- grid-wide barrier of this kernel ---------------------------------------------------------------------------------
 // Same counter protocol as ar_core.cuh grid_barrier.  Warp 0 also refills ring slots right after the arrival.
-// Acquire side: thread 0 polls relaxed and issues ONE fence.acq_rel.gpu once the count is complete; together with the
-// bar.sync that follows, the red.release of every producer CTA synchronizes-with the reads of all threads of this CTA
-// (PTX memory model: fence cumulativity through the CTA barrier).
+// Acquire side: thread 0 polls the counter with ld.acquire.gpu; the poll that returns the full count synchronizes-with
+// the red.release of every producer CTA, and the bar.sync that follows extends that to all threads of this CTA
+// (PTX memory model: causality order through the CTA barrier).  Same-box A/B on C2 (profiles/r02_ab_grid_barrier_acquire.log):
+// relaxed poll without any acquire 629.9 us/step (round 1's variant, formally racy), relaxed poll + fence.acq_rel.gpu
+// 678.7, acquire poll 635.6.
 // `stage` (optional): `nstage` contiguous fp32 vectors of kD floats (LayerNorm gains / biases of the next phase) that
-// warps 4..7 copy into the start of the reduction buffer while thread 0 polls, so the LayerNorm after the barrier
-// reads them from shared memory instead of paying an L2 round trip between its statistics and its output.
+// warps 4..7 copy into the reduction buffer (at float offset stage_off) while thread 0 polls, so the LayerNorm after
+// the barrier reads them from shared memory instead of paying an L2 round trip between its statistics and its output.
 __device__ __forceinline__ bool dec_grid_barrier(const Params& P, const Smem& sm, uint32_t& epoch, Feeder& fd, int extra,
-                                                 int prof_slot = -1, const float* stage = nullptr, int nstage = 0) {
+                                                 int prof_slot = -1, const float* stage = nullptr, int nstage = 0, int stage_off = 0) {
   Ctrl* c = sm.ctrl;
   // bring-up: arrival / release time of every CTA at the three barriers of one layer (scripts/stage_prof.py)
   const bool rec = P.prof && prof_slot >= 0 && threadIdx.x == 0;
@@ -642,19 +730,18 @@ __device__ __forceinline__ bool dec_grid_barrier(const Params& P, const Smem& sm
   if (threadIdx.x >= 128 && nstage) {
     const int t = threadIdx.x - 128;                  // 0..127: 16-byte pieces t, t + 128, ...
 #pragma unroll 1
-    for (int k = t; k < nstage * (kD / 4); k += 128) cp_async_cg16(sm.red + 4 * k, stage + 4 * k);
+    for (int k = t; k < nstage * (kD / 4); k += 128) cp_async_cg16(sm.red + stage_off + 4 * k, stage + 4 * k);
     cp_async_wait_all();
   }
   if (threadIdx.x == 0) {
     const uint32_t target = epoch * (uint32_t)P.G;
     const long long t0 = clock64();
     uint32_t spins = 0;
-#ifdef TTS_DEC_ACQUIRE_POLL
-#define TTS_DEC_POLL ld_acquire_u32
+#ifdef TTS_DEC_RELAXED_POLL   // compile-time A/B only (scripts/ab_build.sh): no acquire at all, relies on every cross-CTA read being ld.cg
+    while (ld_relaxed_u32(P.bar_counter) < target) {
 #else
-#define TTS_DEC_POLL ld_relaxed_u32
+    while (ld_acquire_u32(P.bar_counter) < target) {
 #endif
-    while (TTS_DEC_POLL(P.bar_counter) < target) {
       if ((++spins & 255u) == 0) {
         if (c->abort_flag || __ldcg(P.watchdog) || clock64() - t0 > kWatchdogCycles) {
           c->abort_flag = 1;
@@ -663,9 +750,6 @@ __device__ __forceinline__ bool dec_grid_barrier(const Params& P, const Smem& sm
         }
       }
     }
-#if !defined(TTS_DEC_NO_ACQUIRE_FENCE) && !defined(TTS_DEC_ACQUIRE_POLL)   // compile-time A/B only (scripts/ab.sh): the fence-free variant relies on every cross-CTA read being ld.cg
-    fence_acq_rel_gpu();   // acquire side: the consumers' reads after bar.sync are ordered after the producers' red.release
-#endif
   }
   consumer_sync();
   if (rec) P.prof[8192 + blockIdx.x * 8 + prof_slot + 3] = globaltimer_ns();
@@ -673,13 +757,18 @@ __device__ __forceinline__ bool dec_grid_barrier(const Params& P, const Smem& sm
 }
 
 // ---- the kernel ------------------------------------------------------------------------------------------------
+template <int MODE>
 __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_constant__ Params P) {
+  using C = DecCfg<MODE>;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  const Smem sm = carve_smem(smem_raw, 1);
+  const Smem sm = carve_smem(smem_raw, C::kMtSmem);
   Ctrl* c = sm.ctrl;
   const int rank = (int)cluster_ctarank();
   const int head = (int)cluster_id_x() >> 1;
-  const int row_lo = ((int)cluster_id_x() & 1) * 8;
+  const int row_lo = ((int)cluster_id_x() & 1) * C::kRowsA;       // first row of its head this cluster owns
+  const int tile_row0 = C::kHalf ? 0 : row_lo;                    // first row of the m-tile(s) it multiplies
+  const int attn_row0 = row_lo + C::kAttnRows * rank;             // first attention row of this CTA
+  const int ctx_row0 = attn_row0 - tile_row0;
   Feeder fd;
   fd.head = head; fd.rank = rank; fd.pending = 0;
   tile_range(P.v_tiles, P.G, 0, blockIdx.x, &fd.ht0, &fd.hcnt);
@@ -692,7 +781,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
   }
   __syncthreads();
   if (threadIdx.x < 32) {
-    feed_init(P, fd.f, fd.hcnt);
+    feed_init(P, fd.f, fd.hcnt, C::kGroups);
     feed(P, c, sm.ring, fd.f, P.n_slots, head, rank, fd.ht0, fd.hcnt);
   }
   cluster_sync_all();          // all CTAs of the cluster are running before anyone writes into a peer's shared memory
@@ -704,6 +793,8 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
   bool alive = true;
   const int n = P.n_rows;
   const int ht0 = fd.ht0, hcnt = fd.hcnt;
+  constexpr int kNpcB = 4 * C::kMtB;            // rows per CTA in the LayerNorm of a phase-B / head row group
+  constexpr int kNpcA = C::kLnRowsA / kClusterSize;
   Instr ins;
   ins.row0 = 0; ins.nrows = n; ins.flags = 0; ins.rot = 0; ins.pad0 = ins.pad1 = 0;
   for (int step = 0; step < P.n_steps && alive; ++step) {
@@ -720,7 +811,6 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
     // layer == n_layers is the head: ln_f + final_norm through the same LayerNorm code as ln_1, then the vocabulary GEMM
     for (int layer = 0; layer <= P.n_layers && alive; ++layer) {
       const bool is_head = layer == P.n_layers;
-      ins.layer = is_head ? 0 : layer;
       // ---- phase A: ln_1 -> q,k,v of this head -> attention -> split-K c_proj -> y ----
       prof_mark(P, c, 100 + (is_head ? OP_HEAD : OP_LN_QKV));
       const int pslot = (step == P.prof_step && layer == 3) ? 0 : -4;
@@ -729,10 +819,28 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       if (!alive) break;
       prof_mark(P, c, 200 + (is_head ? OP_HEAD : OP_LN_QKV));
       if (layer == 0 && ld_cg_i(P.n_active) == 0) { alive = false; break; }
-      ins.op = is_head ? OP_HEAD : OP_LN_QKV; ins.flags = 0;
-      ProjAdd padd;
-      if (!is_head) proj_preload(P, layer, head, rank, row_lo, padd);
-      ln_cluster(P, ins, sm, P.x, sm.red, is_head, rank, head, is_head ? 0 : layer + 1, layer == 0 ? row_lo + 2 * rank : -1);
+      {
+        // row facts of the step (layer 0) and the L2 prefetch of the next layer's K/V pages and small parameters: by the
+        // warps the LayerNorm leaves idle (4 rows per CTA: warps 4..7), or by everyone before it (8 rows per CTA)
+        const int pf_layer = is_head ? 0 : layer + 1;
+        const int ln_warps = is_head ? kNpcB : kNpcA;
+        if (kNpcA == 8) {                // MODE 4: every warp normalises in phase A
+          if (layer == 0) {
+            build_rinfo<MODE>(P, tile_row0, attn_row0, sm, threadIdx.x, kDecThreads);
+            consumer_sync();
+          }
+          prefetch_next<MODE>(P, sm, head, pf_layer, threadIdx.x, kDecThreads);
+        } else if (ln_warps == 8) {      // MODE 2 head: all 8 warps normalise (layer != 0); the prefetch goes first
+          prefetch_next<MODE>(P, sm, head, pf_layer, threadIdx.x, kDecThreads);
+        } else if (threadIdx.x >= 128) {
+          if (layer == 0) {
+            build_rinfo<MODE>(P, tile_row0, attn_row0, sm, threadIdx.x - 128, 128);
+            asm volatile("bar.sync 2, 128;" ::: "memory");
+          }
+          prefetch_next<MODE>(P, sm, head, pf_layer, threadIdx.x - 128, 128);
+        }
+        ln_cluster(P, sm, false, sm.red, is_head, rank, is_head ? 0 : tile_row0, ln_warps);
+      }
       cluster_barrier();
       prof_mark(P, c, 1);
       if (is_head) break;
@@ -740,62 +848,89 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
         const float* bias = layer_f(P, layer) + kFOffBqkv;
         const int* ri = rinfo_ptr(sm);
         const int t0 = head * 8 + 2 * rank;
-        gemm16<6, true, false>(P, sm, pipe, fd, 6, row_lo, bias, [&](int i) { return t0 + (i >> 1) * (kD / 8) + (i & 1); },
-                        [&](int row, int col, float v0, float v1) {
+        gemm16<6, C::kMtA, C::kHalf, false>(P, sm, pipe, fd, 6, row_lo, bias, true, [&](int i) { return t0 + (i >> 1) * (kD / 8) + (i & 1); },
+                        [&](int lrow, int col, float v0, float v1) {
+                          const int row = tile_row0 + lrow;
                           if (row >= n) return;
                           const int part = col >> 10, cc = col & (kD - 1);
                           if (part == 0) {   // query, pre-scaled by 1/sqrt(64) (exact: power of two)
                             *reinterpret_cast<float2*>(P.q + (size_t)row * kD + cc) = make_float2(v0 * 0.125f, v1 * 0.125f);
                           } else {           // key / value -> page slot of this row's new position (row facts of the step)
-                            const int page = ri[row];
+                            const int page = ri[lrow];
                             if (page < 0) return;
-                            __nv_bfloat16* dst = P.kv + kv_row_offset(layer, P.n_pages, page, part - 1, cc >> 6, ri[16 + row]) + (cc & 63);
+                            __nv_bfloat16* dst = P.kv + kv_row_offset(layer, P.n_pages, page, part - 1, cc >> 6, ri[32 + lrow]) + (cc & 63);
                             *reinterpret_cast<uint32_t*>(dst) = pack_bf16x2(v0, v1);
                           }
                         });
       }
       cluster_barrier();
       prof_mark(P, c, 200 + OP_ATTN);
-      attn_local(P, layer, head, row_lo + 2 * rank, sm);
+      attn_local<MODE>(P, layer, head, attn_row0, ctx_row0, sm);
       cluster_barrier();
       prof_mark(P, c, 200 + OP_PROJ);
-      proj_splitk(P, layer, head, rank, row_lo, sm, pipe, padd);
+      proj_splitk<MODE>(P, rank, row_lo, tile_row0, sm, pipe);
       // ---- phase B: ln_2 -> c_fc -> gelu_new ----
       prof_mark(P, c, 100 + OP_LN_FC);
-      alive = dec_grid_barrier(P, sm, epoch, fd, 2, pslot + 1, layer_f(P, layer) + kFOffLn2g, 2);   // + the two split-K c_proj slots
+      alive = dec_grid_barrier(P, sm, epoch, fd, 2, pslot + 1, layer_f(P, layer) + kFOffLn2g, 2, kStageOffLn2);   // + the two split-K c_proj slots
       if (!alive) break;
       prof_mark(P, c, 200 + OP_LN_FC);
-      ins.op = OP_LN_FC; ins.flags = F_FIXED_SRC;
-      ln_cluster(P, ins, sm, P.x, sm.red, false, rank, head, -1, -1);
-      cluster_barrier();
-      prof_mark(P, c, 1);
-      {
+#pragma unroll 1
+      for (int grp = 0; grp < C::kGroups; ++grp) {
+        if (grp) cluster_barrier();       // every CTA of the cluster has multiplied the previous group's rows
+        const int rbase = 16 * C::kMtB * grp;
+        ln_cluster(P, sm, true, sm.red + kStageOffLn2, false, rank, rbase, kNpcB);
+        cluster_barrier();
+        prof_mark(P, c, 1);
         const float* bias = layer_f(P, layer) + kFOffBfc;
         const int t0 = blockIdx.x * 4;
-        gemm16<4, false, false>(P, sm, pipe, fd, 4, 0, bias, [&](int i) { return t0 + i; }, [&](int row, int col, float v0, float v1) {
-          if (row >= n) return;
-          const float h0 = gelu_new(v0), h1 = gelu_new(v1);
-          *reinterpret_cast<uint32_t*>(P.hbuf + afrag_elem_offset(row, col, kD4)) = pack_bf16x2(h0, h1);
-        });
+        gemm16<4, C::kMtB, false, false>(P, sm, pipe, fd, 4, 0, bias, grp == C::kGroups - 1, [&](int i) { return t0 + i; },
+                                         [&](int lrow, int col, float v0, float v1) {
+                                           const int row = rbase + lrow;
+                                           if (row >= n) return;
+                                           const float h0 = gelu_new(v0), h1 = gelu_new(v1);
+                                           *reinterpret_cast<uint32_t*>(P.hbuf + afrag_elem_offset(row, col, kD4)) = pack_bf16x2(h0, h1);
+                                         });
       }
       // ---- phase C: mlp.c_proj, x = y + . ----
       prof_mark(P, c, 100 + OP_PROJ2);
       alive = dec_grid_barrier(P, sm, epoch, fd, 0, pslot + 2);
       if (!alive) break;
       prof_mark(P, c, 200 + OP_PROJ2);
-      proj2_stage(P, layer, sm, pipe, fd, rank);
+#pragma unroll 1
+      for (int grp = 0; grp < C::kGroups; ++grp) proj2_stage<MODE>(P, layer, sm, pipe, fd, rank, grp, grp == C::kGroups - 1);
       if (c->abort_flag) alive = false;
     }
     if (!alive) break;
-    for (int tb = 0; tb < hcnt; tb += 6) {
-      const int t0 = ht0 + tb;
-      gemm16<6, false, true>(P, sm, pipe, fd, min(6, hcnt - tb), 0, P.b_head, [&](int i) { return t0 + i; },
-                       [&](int row, int col, float v0, float v1) {
-                         if (row >= n) return;
-                         float* lp = P.logits + (size_t)row * P.v_stride + col;     // b_head is zero-padded to v_stride
-                         if (col < P.V) lp[0] = v0;
-                         if (col + 1 < P.V) lp[1] = v1;
-                       });
+    // ---- mel head: logits of every row group (group 0 was normalised by the layer loop's last iteration) ----
+#pragma unroll 1
+    for (int grp = 0; grp < C::kGroups; ++grp) {
+      const int rbase = 16 * C::kMtB * grp;
+      if (grp) {
+        cluster_barrier();                // the previous group's rows have been multiplied by every CTA of the cluster
+        // the staged ln_f / final_norm gains were overwritten by the reduction: stage them again
+        for (int k = threadIdx.x; k < 4 * (kD / 4); k += kDecThreads) cp_async_cg16(sm.red + 4 * k, P.lnf_g + 4 * k);
+        cp_async_wait_all();
+        consumer_sync();
+        ln_cluster(P, sm, false, sm.red, true, rank, rbase, kNpcB);
+        cluster_barrier();
+      }
+      for (int tb = 0; tb < hcnt; tb += 6) {
+        const int t0 = ht0 + tb;
+        gemm16<6, C::kMtB, false, true>(P, sm, pipe, fd, min(6, hcnt - tb), 0, P.b_head, true, [&](int i) { return t0 + i; },
+                         [&](int lrow, int col, float v0, float v1) {
+                           const int row = rbase + lrow;
+                           if (row >= n) return;
+                           float* lp = P.logits + (size_t)row * P.v_stride + col;     // b_head is zero-padded to v_stride
+                           if (col < P.V) lp[0] = v0;
+                           if (col + 1 < P.V) lp[1] = v1;
+                         });
+        // a CTA's head tiles (8 or 9 chunks, per row group) are more than the ring holds ahead at this point when it has 8
+        // slots: refill here, not only at the next grid barrier (the reduction's trailing CTA barrier has passed: the
+        // slots are free)
+        const int refill_n = min(fd.pending, 6);
+        fd.pending -= refill_n;
+        if (threadIdx.x < 32 && refill_n) feed(P, c, sm.ring, fd.f, refill_n, fd.head, fd.rank, fd.ht0, fd.hcnt);
+      }
     }
     if (c->abort_flag) alive = false;
   }
@@ -835,13 +970,23 @@ void launch_pack_projk(const void* src, int dtype, uint4* dst, cudaStream_t st) 
     pack_projk_kernel<__nv_bfloat16><<<512, 256, 0, st>>>((const __nv_bfloat16*)src, dst);
 }
 
-static cudaError_t decode_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attrs, int smem_bytes, int device, bool cooperative,
+// ---- launch ----------------------------------------------------------------------------------------------------------
+typedef void (*DecKernel)(const Params);
+static DecKernel decode_kernel_of(int mode) {
+  return mode == 1 ? (DecKernel)ar_decode_kernel<1> : mode == 2 ? (DecKernel)ar_decode_kernel<2> : (DecKernel)ar_decode_kernel<4>;
+}
+
+int decode_mode_for(int n_rows) { return n_rows <= 16 ? 1 : n_rows <= 32 ? 2 : 4; }
+int decode_mt_smem(int mode) { return mode == 1 ? 1 : 2; }
+
+static cudaError_t decode_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attrs, int mode, int smem_bytes, int device, bool cooperative,
                                  cudaStream_t st) {
-  static unsigned long long attr_set = 0;   // one bit per device ordinal: the opt-in is per device
-  if (!(attr_set >> (device & 63) & 1ull)) {
-    cudaError_t e = cudaFuncSetAttribute(ar_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+  static unsigned long long attr_set[3] = {0, 0, 0};   // one bit per device ordinal: the opt-in is per device
+  const int mi = mode == 1 ? 0 : mode == 2 ? 1 : 2;
+  if (!(attr_set[mi] >> (device & 63) & 1ull)) {
+    cudaError_t e = cudaFuncSetAttribute((const void*)decode_kernel_of(mode), cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
     if (e != cudaSuccess) return e;
-    attr_set |= 1ull << (device & 63);
+    attr_set[mi] |= 1ull << (device & 63);
   }
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(kDecCtas);
@@ -860,22 +1005,23 @@ static cudaError_t decode_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* a
   return cudaSuccess;
 }
 
-cudaError_t launch_decode(const Params& P, int smem_bytes, int device, bool cooperative, cudaStream_t st) {
+cudaError_t launch_decode(const Params& P, int mode, int smem_bytes, int device, bool cooperative, cudaStream_t st) {
   cudaLaunchConfig_t cfg;
   cudaLaunchAttribute attrs[2];
-  cudaError_t e = decode_config(cfg, attrs, smem_bytes, device, cooperative, st);
+  cudaError_t e = decode_config(cfg, attrs, mode, smem_bytes, device, cooperative, st);
   if (e != cudaSuccess) return e;
-  return cudaLaunchKernelEx(&cfg, ar_decode_kernel, P);
+  void* args[] = {const_cast<Params*>(&P)};
+  return cudaLaunchKernelExC(&cfg, (const void*)decode_kernel_of(mode), args);
 }
 
-// Clusters of kClusterSize CTAs (1 CTA / SM at this shared-memory size) that can be co-resident; the kernel needs kDecClusters.
-int decode_max_clusters(int smem_bytes, int device) {
+// Clusters of kClusterSize CTAs (1 CTA / SM at this shared-memory size) that can be co-resident; the kernels need kDecClusters.
+int decode_max_clusters(int mode, int smem_bytes, int device) {
   cudaLaunchConfig_t cfg;
   cudaLaunchAttribute attrs[2];
-  if (decode_config(cfg, attrs, smem_bytes, device, true, 0) != cudaSuccess) { cudaGetLastError(); return 0; }
+  if (decode_config(cfg, attrs, mode, smem_bytes, device, true, 0) != cudaSuccess) { cudaGetLastError(); return 0; }
   cfg.numAttrs = 1;   // the occupancy query takes the cluster dimension only
   int n = 0;
-  cudaError_t e = cudaOccupancyMaxActiveClusters(&n, ar_decode_kernel, &cfg);
+  cudaError_t e = cudaOccupancyMaxActiveClusters(&n, (const void*)decode_kernel_of(mode), &cfg);
   if (e != cudaSuccess) {
     if (getenv("TTS_AR_VERBOSE")) fprintf(stderr, "[tts_ar] cudaOccupancyMaxActiveClusters: %s\n", cudaGetErrorString(e));
     cudaGetLastError();

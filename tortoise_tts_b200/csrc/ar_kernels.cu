@@ -202,7 +202,7 @@ void launch_embed_rows(const EmbedArgs& a, int n_rows, cudaStream_t st) { embed_
 
 // ---- sampler state reset after a prompt pass (fake_inputs = [1]*P + [start_mel], unified_voice.py:647-649) ----
 __global__ void reset_sampler_kernel(int n_seqs, int seen_words, uint32_t* seen, int* finished, int* gen_count,
-                                     int* row_pos, int* n_active, int start_mel, int* attn_cnt, int n_cnt) {
+                                     int* row_pos, int* n_active, int group_size, int start_mel, int* attn_cnt, int n_cnt) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n_seqs * seen_words) {
     const int wd = i % seen_words;
@@ -217,20 +217,17 @@ __global__ void reset_sampler_kernel(int n_seqs, int seen_words, uint32_t* seen,
     row_pos[i] = -1;
   }
   if (i < n_cnt) attn_cnt[i] = 0;
-  if (i == 0) {
-    n_active[0] = n_seqs;
-    // 16-sequence groups of a 17..32-sequence batch run as consecutive head-cluster launches (tts_ar_run.cu run_steps)
-    n_active[1] = min(n_seqs, kDecRows);
-    n_active[2] = max(0, min(n_seqs - kDecRows, kDecRows));
-  }
+  if (i == 0) n_active[0] = n_seqs;
+  // groups of a batch larger than one head-cluster launch run as consecutive launches (tts_ar_run.cu run_steps)
+  if (i * group_size < n_seqs) n_active[1 + i] = min(group_size, n_seqs - i * group_size);
 }
 
 void launch_reset_sampler(int n_seqs, int seen_words, uint32_t* seen, int* finished, int* gen_count, int* row_pos,
-                          int* n_active, int start_mel, int* attn_cnt, int n_cnt, cudaStream_t st) {
+                          int* n_active, int group_size, int start_mel, int* attn_cnt, int n_cnt, cudaStream_t st) {
   int n = n_seqs * seen_words;
   if (n_cnt > n) n = n_cnt;
   reset_sampler_kernel<<<(n + 255) / 256, 256, 0, st>>>(n_seqs, seen_words, seen, finished, gen_count, row_pos, n_active,
-                                                        start_mel, attn_cnt, n_cnt);
+                                                        group_size, start_mel, attn_cnt, n_cnt);
 }
 
 // ---- stop-token fix-up + calm-token trim of the generated codes (reference inference.py:353-366, 381-389; the same

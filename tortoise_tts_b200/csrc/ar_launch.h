@@ -27,13 +27,16 @@ void launch_embed_rows(const EmbedArgs& a, int n_rows, cudaStream_t st);
 void launch_fixup_codes(long long* codes, int rows, int len, int stride, int stop, int calm, int* first_stop, int* trim,
                         cudaStream_t st);
 void launch_reset_sampler(int n_seqs, int seen_words, uint32_t* seen, int* finished, int* gen_count, int* row_pos,
-                          int* n_active, int start_mel, int* attn_cnt, int n_cnt, cudaStream_t st);
+                          int* n_active, int group_size, int start_mel, int* attn_cnt, int n_cnt, cudaStream_t st);
 void launch_fill_i64(long long* p, size_t n, long long v, cudaStream_t st);
 cudaError_t launch_program(const Params& P, int smem_bytes, int device, cudaStream_t st);
 int program_max_ctas_per_sm(int smem_bytes);
 // head-cluster decode kernel (ar_decode.cu)
 void launch_pack_projk(const void* src, int dtype, uint4* dst, cudaStream_t st);
-cudaError_t launch_decode(const Params& P, int smem_bytes, int device, bool cooperative, cudaStream_t st);
-int decode_max_clusters(int smem_bytes, int device);
+// mode = 16-row m-tiles per launch (1, 2, 4: <= 16, 32, 64 sequences)
+int decode_mode_for(int n_rows);
+int decode_mt_smem(int mode);
+cudaError_t launch_decode(const Params& P, int mode, int smem_bytes, int device, bool cooperative, cudaStream_t st);
+int decode_max_clusters(int mode, int smem_bytes, int device);
 
 }  // namespace tts

@@ -112,6 +112,7 @@ struct Params {
   float typical_mass;            // TypicalLogitsWarper mass in (0,1); 0 = off
   unsigned long long seed;
   long long seq_index_base;
+  const long long* seq_indices;   // nullable [seqs]: global sequence index per local sequence (overrides seq_index_base + seq)
   int stop_token;
   int max_pos_rows;      // rows of mel_pos (bounds guard)
   // outputs

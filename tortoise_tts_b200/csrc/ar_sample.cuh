@@ -367,7 +367,8 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
       if (i < w) wbase += t;
       total += t;
     }
-    const float u01 = philox_uniform(P.seed, (uint32_t)(P.seq_index_base + seq), (uint32_t)gen);
+    const long long gseq = P.seq_indices ? P.seq_indices[seq] : P.seq_index_base + seq;
+    const float u01 = philox_uniform(P.seed, (uint32_t)gseq, (uint32_t)gen);
     const float target = u01 * total;
     float run = wbase + incl - loc;
     int found = 0x7fffffff, lastkept = -1;
@@ -425,9 +426,18 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
   const float4* e4 = reinterpret_cast<const float4*>(P.mel_emb + (size_t)tok * kD);
   const float4* p4 = reinterpret_cast<const float4*>(P.mel_pos + (size_t)pidx * kD);
   float4* x4 = reinterpret_cast<float4*>(P.x + (size_t)seq * kD);
+  // head-cluster kernels (P.y != nullptr): the attention block of layer 0 accumulates onto y = x + attn.c_proj bias
+  const float4* b4 = P.y ? reinterpret_cast<const float4*>(layer_f(P, 0) + kFOffBproj) : nullptr;
   for (int i = tid; i < kD / 4; i += kConsumerThreads) {
     const float4 a = e4[i], b = p4[i];
-    x4[i] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+    const float4 xv = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+    x4[i] = xv;
+    if (b4) {
+      const float4 bb = b4[i];
+      longlong2* y2 = reinterpret_cast<longlong2*>(P.y + (size_t)seq * kD + 4 * i);
+      y2[0] = make_longlong2(to_fixed(xv.x + bb.x), to_fixed(xv.y + bb.y));
+      y2[1] = make_longlong2(to_fixed(xv.z + bb.z), to_fixed(xv.w + bb.w));
+    }
   }
   consumer_sync();   // sc / ev / scratch are reused by the next row
   prof_mark(P, c, 35);

@@ -92,7 +92,8 @@ TTS_HD int next_rot(int n_tiles, int G, int rot) { return (rot + n_tiles % G) % 
 constexpr int kClusterSize = 4;
 constexpr int kDecClusters = 2 * kH;
 constexpr int kDecCtas = kClusterSize * kDecClusters;   // 128
-constexpr int kDecRows = 16;                            // rows (sequences) the cluster kernel handles
+constexpr int kDecRows = 16;                            // rows (sequences) of one m-tile of the cluster kernels
+constexpr int kDecMaxRows = 64;                         // most rows one launch of them handles (MODE 4); larger batches run as groups
 constexpr int kProjkChunks = kH * 8;                    // split-K chunks per layer: (head, 128-column block)
 // attn.c_proj split-K chunk (16 KiB) of (head h, column block cb): W[64h + k][128cb + n], k < 64, n < 128, stored
 //   chunk[tile (16)][s (2)][lane (32)] = uint4 { b0(kb=2s), b1(kb=2s), b0(kb=2s+1), b1(kb=2s+1) }

@@ -59,13 +59,13 @@ static int create_impl(TtsArHandle* h) {
   h->nqp = (c.max_new_tokens + kPage - 1) / kPage;
   const int rf_len = c.max_text_len + c.max_new_tokens + 5;   // latent + (T+2) + (M+2)
   if (rf_len > kMaxPagesPerSeg * kPage) return fail(h, TTS_AR_ERR_BAD_ARG, "max_text_len + max_new_tokens + 5 exceeds 1024 positions");
-  const int rf_batch = std::max(1, std::min(c.max_seqs, 16384 / rf_len));
+  const int rf_batch = std::max(1, std::min(c.max_seqs, 65536 / rf_len));
   h->rf_rows_cap = rf_batch * rf_len;
   const int rf_pages = rf_batch * ((rf_len + kPage - 1) / kPage);
   h->n_pages = std::max(c.max_utts * h->npp + c.max_seqs * h->nqp, rf_pages);
   h->rows_cap = std::max({c.max_seqs, c.max_utts * h->plen_max, h->rf_rows_cap});
   h->rows_cap = (h->rows_cap + 127) / 128 * 128;    // 128-row GEMM instructions read whole m-tiles
-  h->logit_rows_cap = (std::max(c.max_seqs, c.max_utts) + 63) / 64 * 64;
+  h->logit_rows_cap = (std::max(c.max_seqs, c.max_utts) + 63) / 64 * 64 + (c.max_utts + 63) / 64 * 64;   // + the prompt-pass rows kept for later groups
   h->plan_cap_units = std::max(h->G * kNW, 1);
   h->seen_words = (c.n_mel_codes + 31) / 32;
   h->v_tiles = (c.n_mel_codes + 7) / 8;
@@ -107,7 +107,7 @@ static int create_impl(TtsArHandle* h) {
 
   DALLOC(h, h->d_x, (size_t)h->rows_cap * kD);
   DALLOC(h, h->d_q, (size_t)h->rows_cap * kD);
-  DALLOC(h, h->d_y, (size_t)kDecRows * kD);
+  DALLOC(h, h->d_y, (size_t)kDecMaxRows * kD);
   DALLOC(h, h->d_ctx, (size_t)h->rows_cap * kD);
   DALLOC(h, h->d_xn, (size_t)h->rows_cap * kD);
   DALLOC(h, h->d_h, (size_t)h->rows_cap * kD4);
@@ -132,15 +132,15 @@ static int create_impl(TtsArHandle* h) {
   DALLOC(h, h->d_plan, 8 + c.max_seqs + 1);
   DALLOC(h, h->d_finished, c.max_seqs);
   DALLOC(h, h->d_gen_count, c.max_seqs);
-  DALLOC(h, h->d_n_active, 4);
+  DALLOC(h, h->d_n_active, 4 + kMaxGroups);
   DALLOC(h, h->d_seen, (size_t)c.max_seqs * h->seen_words);
   DALLOC(h, h->d_bar, 4);
   DALLOC(h, h->d_watchdog, 4);
-  DALLOC(h, h->d_steps_done, 4);
+  DALLOC(h, h->d_steps_done, 4 + kMaxGroups);
   DALLOC(h, h->d_in_latent, (size_t)c.max_utts * kD);
   DALLOC(h, h->d_in_text, (size_t)c.max_utts * std::max(c.max_text_len, 1));
   DALLOC(h, h->d_out_codes, (size_t)c.max_seqs * std::max(c.max_new_tokens, 1));
-  TTS_CUDA(h, cudaMallocHost(&h->h_pinned_i, 64));
+  TTS_CUDA(h, cudaMallocHost(&h->h_pinned_i, sizeof(int) * (8 + 2 * kMaxGroups)));
   // staging for the per-call index uploads: page tables, lengths, row maps (all int32)
   h->staging_bytes = sizeof(int) * ((size_t)pt_rows * (kMaxPagesPerSeg + 4) + 3 * (size_t)h->rows_cap + (size_t)h->logit_rows_cap +
                                     (size_t)c.max_seqs * (kMaxPagesPerSeg + 2)) + 4096;
@@ -158,8 +158,12 @@ static int create_impl(TtsArHandle* h) {
   const int smem1 = smem_total_bytes(1, smem_max_slots(1, h->smem_budget));
   if (program_max_ctas_per_sm(smem1) < 1) return fail(h, TTS_AR_ERR_DEVICE, "interpreter kernel does not fit on an SM");
   {
+    int ncl = 1 << 30;
+    for (int mode = 1; mode <= 4; mode *= 2) {
+      const int mt = decode_mt_smem(mode);
+      ncl = std::min(ncl, decode_max_clusters(mode, smem_total_bytes(mt, smem_max_slots(mt, h->smem_budget)), c.device));
+    }
     const int smemd = smem_total_bytes(1, smem_max_slots(1, h->smem_budget));
-    const int ncl = decode_max_clusters(smemd, c.device);
     h->use_cluster = ncl >= kDecClusters;
     if (getenv("TTS_AR_VERBOSE")) fprintf(stderr, "[tts_ar] co-resident clusters of %d CTAs: %d (smem %d B) -> decode kernel: %s\n",
                                           kClusterSize, ncl, smemd, h->use_cluster ? "head-cluster" : "interpreter");
@@ -179,7 +183,7 @@ extern "C" int tts_ar_create(const TtsArConfig* cfg, TtsArHandle** out) {
   if (cfg->n_layers < 1 || cfg->n_mel_codes < 2 || cfg->n_mel_codes > 8256 || cfg->max_utts < 1 || cfg->max_seqs < cfg->max_utts ||
       cfg->max_text_len < 1 || cfg->max_text_len + 2 > cfg->n_text_pos || cfg->max_new_tokens < 1 ||
       cfg->max_new_tokens + 2 > cfg->n_mel_pos || cfg->stop_mel_token >= cfg->n_mel_codes || cfg->start_mel_token >= cfg->n_mel_codes ||
-      cfg->start_text_token >= cfg->n_text_rows || cfg->max_seqs > 1024)
+      cfg->start_text_token >= cfg->n_text_rows || cfg->max_seqs > kDecMaxRows * kMaxGroups)
     return fail(nullptr, TTS_AR_ERR_BAD_ARG, "TtsArConfig out of range");
   TtsArHandle* h = new TtsArHandle();
   h->cfg = *cfg;

@@ -23,6 +23,8 @@ struct DenseW {
   CUtensorMap a_xn, a_ctx, a_h;       // activation buffers as A operands (row-major bf16 in this path)
 };
 
+constexpr int kMaxGroups = 16;   // a batch runs as at most this many consecutive head-cluster launches of <= 64 sequences
+
 struct TtsArHandle {
   TtsArConfig cfg{};
   int G = 0;                 // CTAs == SMs
@@ -75,7 +77,7 @@ struct TtsArHandle {
   float* d_in_latent = nullptr;
   int* d_in_text = nullptr;
   long long* d_out_codes = nullptr;
-  bool grouped = false;          // last run_steps ran 16-sequence groups as consecutive head-cluster launches
+  int n_groups = 1;              // head-cluster launches (groups of <= 64 sequences) the last run_steps used; 0: interpreter
   int *h_pinned_i = nullptr;     // pinned int scratch: [0]=steps_done [1]=watchdog
   long long* h_pinned_codes = nullptr;
   float* h_pinned_latent = nullptr;

@@ -51,12 +51,13 @@ static int launch(TtsArHandle* h, Params& P, cudaStream_t st, bool cluster = fal
   TTS_CUDA(h, cudaMemsetAsync(h->d_bar, 0, sizeof(unsigned int), st));
   cudaError_t e;
   if (cluster) {
+    const int mode = decode_mode_for(P.n_rows);
     P.G = kDecCtas;
     P.y = h->d_y;
-    P.mt_max = 1;
-    P.n_slots = smem_max_slots(1, h->smem_budget);
-    TTS_CUDA(h, cudaMemsetAsync(h->d_y, 0, sizeof(long long) * kDecRows * kD, st));
-    e = launch_decode(P, smem_total_bytes(1, P.n_slots), h->cfg.device, decode_cooperative(h), st);
+    P.mt_max = decode_mt_smem(mode);
+    P.n_slots = smem_max_slots(P.mt_max, h->smem_budget);
+    TTS_CUDA(h, cudaMemsetAsync(h->d_y, 0, sizeof(long long) * kDecRows * mode * kD, st));
+    e = launch_decode(P, mode, smem_total_bytes(P.mt_max, P.n_slots), h->cfg.device, decode_cooperative(h), st);
     if (e != cudaSuccess) return cuda_fail(h, e, "cudaLaunchKernelEx(ar_decode_kernel)");
     h->launches += 1;
     return 0;
@@ -212,7 +213,7 @@ extern "C" int tts_ar_prefill(TtsArHandle* h, const float* latent, const int32_t
   rc = sg.done();
   if (rc) return rc;
   launch_reset_sampler(h->n_seqs, h->seen_words, h->d_seen, h->d_finished, h->d_gen_count, h->d_seq_pos, h->d_n_active,
-                       c.start_mel_token, h->d_attn_cnt, h->n_seqs * kH, st);
+                       kDecMaxRows, c.start_mel_token, h->d_attn_cnt, h->n_seqs * kH, st);
   h->launches += 1;
   h->dec_mt_max = mt_max_for(h->n_seqs);
   TTS_CUDA(h, cudaEventRecord(h->ev1, st));
@@ -248,32 +249,36 @@ static int run_steps(TtsArHandle* h, const TtsArSampling* s, int n_steps, bool s
   P.do_sample = s->do_sample; P.top_k = s->top_k; P.ignore_eos = s->ignore_eos;
   P.temperature = s->temperature; P.top_p = s->top_p; P.rep_penalty = s->repetition_penalty;
   P.typical_mass = (s->typical_mass > 0.f && s->typical_mass < 1.f) ? s->typical_mass : 0.f;
-  P.seed = s->seed; P.seq_index_base = s->seq_index_base;
+  P.seed = s->seed; P.seq_index_base = s->seq_index_base; P.seq_indices = (const long long*)s->seq_indices;
   P.out_codes = out_codes; P.out_stride = n_steps; P.out_latents = out_latents; P.forced = forced; P.out_choice = out_choice;
-  // 17..32 sequences: two consecutive launches of the 16-row head-cluster kernel (670 us/step each) beat one pass of the
-  // interpreter over 32 rows (1630 us/step).  Every per-sequence array is a pointer offset; sequences are independent and
-  // the Philox key is the global sequence index, so the result is bit-identical to two separate 16-candidate calls.
-  h->grouped = h->use_cluster && !h->opt_decode_interp && h->n_seqs > kDecRows && h->n_seqs <= 2 * kDecRows;
+  // Up to 64 sequences are ONE launch of a head-cluster kernel (MODE 1 / 2 / 4: every streamed weight chunk is multiplied
+  // with all of the launch's rows).  Larger batches run as consecutive launches over groups of 64: every per-sequence array
+  // is a pointer offset; sequences are independent and the Philox key is the global sequence index, so the result is
+  // bit-identical to separate calls on the groups.
+  const bool cluster = h->use_cluster && !h->opt_decode_interp;
+  h->n_groups = cluster ? (h->n_seqs + kDecMaxRows - 1) / kDecMaxRows : 0;
   int rc = 0;
-  if (h->grouped) {
-    const int stash = 2 * kDecRows;            // logit rows [32, 32 + n_utt): the prompt-pass rows, kept for group 1
+  if (h->n_groups > 1) {
+    const int stash = h->logit_rows_cap - (h->cfg.max_utts + 63) / 64 * 64;   // the prompt-pass rows, kept for every group
     if (h->first_step_pending) {
       TTS_CUDA(h, cudaMemcpyAsync(h->d_logits + (size_t)stash * h->v_stride, h->d_logits, sizeof(float) * h->n_utt * h->v_stride,
                                   cudaMemcpyDeviceToDevice, st));
       TTS_CUDA(h, cudaMemcpyAsync(h->d_cur_latent + (size_t)stash * kD, h->d_cur_latent, sizeof(float) * h->n_utt * kD,
                                   cudaMemcpyDeviceToDevice, st));
     }
-    for (int g = 0; g * kDecRows < h->n_seqs && !rc; ++g) {
-      const int s0 = g * kDecRows, cnt = std::min(kDecRows, h->n_seqs - s0);
+    for (int g = 0; g < h->n_groups && !rc; ++g) {
+      const int s0 = g * kDecMaxRows, cnt = std::min(kDecMaxRows, h->n_seqs - s0);
       Params Q = P;
       Q.n_rows = Q.n_head_rows = Q.n_seqs = cnt;
       Q.x += (size_t)s0 * kD; Q.q += (size_t)s0 * kD;
+      Q.hbuf += (size_t)s0 * kD4;
       Q.logits += (size_t)s0 * h->v_stride; Q.cur_latent += (size_t)s0 * kD;
       Q.logits_pf = h->d_logits + (size_t)stash * h->v_stride; Q.cur_latent_pf = h->d_cur_latent + (size_t)stash * kD;
       Q.row_utt += s0; Q.row_pos += s0; Q.seq_utt += s0; Q.priv_pt += (size_t)s0 * kMaxPagesPerSeg;
       Q.finished += s0; Q.gen_count += s0; Q.seen += (size_t)s0 * h->seen_words;
       Q.n_active = h->d_n_active + 1 + g; Q.steps_done = h->d_steps_done + 1 + g;
       Q.seq_index_base += s0;
+      if (Q.seq_indices) Q.seq_indices += s0;
       Q.out_codes += (size_t)s0 * n_steps;
       if (Q.out_latents) Q.out_latents += (size_t)s0 * n_steps * kD;
       if (Q.forced) Q.forced += (size_t)s0 * n_steps;
@@ -281,7 +286,7 @@ static int run_steps(TtsArHandle* h, const TtsArSampling* s, int n_steps, bool s
       rc = launch(h, Q, st, true);
     }
   } else {
-    rc = launch(h, P, st, h->use_cluster && !h->opt_decode_interp && h->n_seqs <= kDecRows);
+    rc = launch(h, P, st, cluster);
   }
   if (rc) return rc;
   // SURVEY.md 8(d) algorithmic bytes, assuming every sequence stays live (exact under ignore_eos)
@@ -335,14 +340,20 @@ extern "C" int tts_ar_sync_result(TtsArHandle* h, TtsArStats* out, void* stream)
   TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[1], h->d_watchdog, sizeof(int), cudaMemcpyDeviceToHost, st));
   TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[3], h->d_watchdog + 1, sizeof(int), cudaMemcpyDeviceToHost, st));
   TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[2], h->d_n_active, sizeof(int), cudaMemcpyDeviceToHost, st));
-  if (h->grouped) {   // per-group counters: the call ran until its slowest group finished
-    TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[4], h->d_steps_done + 1, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
-    TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[6], h->d_n_active + 1, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+  const int ng = h->n_groups > 1 ? h->n_groups : 0;
+  if (ng) {   // per-group counters: the call ran until its slowest group finished
+    TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[8], h->d_steps_done + 1, ng * sizeof(int), cudaMemcpyDeviceToHost, st));
+    TTS_CUDA(h, cudaMemcpyAsync(&h->h_pinned_i[8 + kMaxGroups], h->d_n_active + 1, ng * sizeof(int), cudaMemcpyDeviceToHost, st));
   }
   TTS_CUDA(h, cudaStreamSynchronize(st));
-  if (h->grouped) {
-    h->h_pinned_i[0] = std::max(h->h_pinned_i[4], h->h_pinned_i[5]);
-    h->h_pinned_i[2] = h->h_pinned_i[6] + h->h_pinned_i[7];
+  if (ng) {
+    int steps = 0, active = 0;
+    for (int g = 0; g < ng; ++g) {
+      steps = std::max(steps, h->h_pinned_i[8 + g]);
+      active += h->h_pinned_i[8 + kMaxGroups + g];
+    }
+    h->h_pinned_i[0] = steps;
+    h->h_pinned_i[2] = active;
   }
   memset(out, 0, sizeof(*out));
   out->struct_size = (int)sizeof(TtsArStats);

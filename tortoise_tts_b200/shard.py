@@ -117,3 +117,65 @@ def gather_codes(codes, pad_token, shards, group=None, latents=None):
             out_lat[idx] = alll[r, : s.n_seqs]
     assert int(shapes[rank, 0]) == codes.shape[0]
     return (out, out_lat) if latents is not None else out
+
+
+# ---- length-balanced utterance shards (BASELINE config C4: ragged text lengths) ---------------------------------------
+def plan_balanced_utterance_shards(text_lens, world):
+    """Utterance-major shards with equal utterance counts (+-1) and balanced prompt lengths: utterances sorted by length,
+    longest first, each handed to the least-loaded rank that still has room (LPT).  All candidates of an utterance stay
+    on one rank (they share its prompt KV pages).  Returns one ascending list of utterance indices per rank.  The shards
+    are not contiguous in the global order: pass `global_sequence_indices(...)` as `seq_indices` so that the sampled
+    codes stay invariant to the world size."""
+    n = len(text_lens)
+    if world < 1:
+        raise ValueError("world must be >= 1")
+    cap = [n // world + (1 if r < n % world else 0) for r in range(world)]
+    load = [0] * world
+    out = [[] for _ in range(world)]
+    for u in sorted(range(n), key=lambda i: (-int(text_lens[i]), i)):
+        r = min((r for r in range(world) if len(out[r]) < cap[r]), key=lambda r: (load[r], r))
+        out[r].append(u)
+        load[r] += int(text_lens[u])
+    return [sorted(x) for x in out]
+
+
+def global_sequence_indices(utts, n_cand):
+    """Global sequence index i = u * n_cand + c of every local sequence of a shard holding utterances `utts`."""
+    return [u * n_cand + c for u in utts for c in range(n_cand)]
+
+
+def gather_rows(local, index_lists, pad_value, group=None):
+    """All-gathers per-rank row blocks [n_r, ...] (same trailing shape up to dim 1, which is padded to the longest with
+    `pad_value`) and returns the global tensor with row index_lists[r][k] = rank r's row k."""
+    world = dist.get_world_size(group)
+    dev = local.device
+    shape = torch.tensor([local.shape[0], local.shape[1] if local.dim() > 1 else 1], dtype=torch.int64, device=dev)
+    shapes = [torch.zeros_like(shape) for _ in range(world)]
+    dist.all_gather(shapes, shape, group=group)
+    shapes = torch.stack(shapes).cpu()
+    max_rows, max_cols = int(shapes[:, 0].max()), int(shapes[:, 1].max())
+    tail = tuple(local.shape[2:])
+    buf = torch.full((max_rows, max_cols) + tail, pad_value, dtype=local.dtype, device=dev)
+    if local.shape[0]:
+        buf[: local.shape[0], : local.shape[1]] = local
+    allbuf = torch.empty((world * max_rows, max_cols) + tail, dtype=local.dtype, device=dev)
+    dist.all_gather_into_tensor(allbuf, buf, group=group)
+    allbuf = allbuf.view((world, max_rows, max_cols) + tail)
+    total = sum(len(x) for x in index_lists)
+    out = torch.full((total, max_cols) + tail, pad_value, dtype=local.dtype, device=dev)
+    for r, idx in enumerate(index_lists):
+        if idx:
+            out[torch.tensor(idx, dtype=torch.long, device=dev)] = allbuf[r, : len(idx)]
+    return out
+
+
+def allgather_inplace(buf, group=None):
+    """`buf` [world, ...]: every rank has already written ITS block buf[rank] (e.g. the latent re-forward writes its
+    output straight into it, `UnifiedVoiceB200.forward(out=buf[rank])`); one NCCL all-gather fills the other blocks in
+    place -- no pack / pad / copy kernel precedes the collective."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    if buf.shape[0] != world or not buf.is_contiguous():
+        raise ValueError("buf must be a contiguous [world, ...] tensor")
+    dist.all_gather_into_tensor(buf.view((-1,) + tuple(buf.shape[2:])) if buf.dim() > 2 else buf.view(-1), buf[rank], group=group)
+    return buf

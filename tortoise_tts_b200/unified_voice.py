@@ -187,6 +187,10 @@ class UnifiedVoiceB200:
         s.repetition_penalty = 1.0 if r is None else float(r)
         s.seed = int(kw.pop("seed", 0))              # reference generate(seed=0), stream_generator.py:223
         s.seq_index_base = int(kw.pop("seq_index_base", 0))
+        idx = kw.pop("seq_indices", None)          # global index per local sequence (non-contiguous shards, shard.py)
+        if idx is not None:
+            self._seq_indices = torch.as_tensor(idx, dtype=torch.int64).to(self.device).contiguous()   # kept alive for the call
+            s.seq_indices = self._seq_indices.data_ptr()
         s.ignore_eos = 1 if kw.pop("ignore_eos", False) else 0
         # reference: LogitsProcessorList([TypicalLogitsWarper(mass=typical_mass)]) if typical_sampling (:659)
         tm = kw.pop("typical_mass", None)
@@ -323,7 +327,8 @@ class UnifiedVoiceB200:
                 return
 
     def forward(self, speech_conditioning_latent, text_inputs, text_lengths, mel_codes, wav_lengths, types=None,
-                text_first=True, raw_mels=None, return_attentions=False, return_latent=False, clip_inputs=True):
+                text_first=True, raw_mels=None, return_attentions=False, return_latent=False, clip_inputs=True, out=None,
+                ragged_text=False):
         if not return_latent or not text_first or raw_mels is not None or types is not None or return_attentions:
             raise NotImplementedError("only forward(..., return_latent=True, text_first=True) is on the AR inference path")
         n = mel_codes.shape[0]
@@ -353,8 +358,13 @@ class UnifiedVoiceB200:
         codes = codes.to(torch.int32).contiguous()
         lat = speech_conditioning_latent.detach().to(device=self.device, dtype=torch.float32).contiguous()
         txt = text_inputs.detach().to(device=self.device, dtype=torch.int32).contiguous()
-        out = torch.zeros((n, M, self.geometry.model_dim), dtype=torch.float32, device=self.device)
-        tl = (C.c_int32 * n)(*([T] * n))
+        if out is None:
+            out = torch.zeros((n, M, self.geometry.model_dim), dtype=torch.float32, device=self.device)
+        elif out.shape != (n, M, self.geometry.model_dim) or out.dtype != torch.float32 or not out.is_contiguous() or out.device != self.device:
+            raise ValueError("out must be a contiguous float32 [n, M, 1024] tensor on the model's device")   # e.g. this rank's slice of an all-gather buffer
+        # reference semantics: padded text is NOT masked (quirk Q8) -> every row runs at the full width T; ragged_text=True
+        # is the extension that runs each row at its own text_lengths[i] (what a ragged inference_speech batch produced)
+        tl = (C.c_int32 * n)(*([int(x) for x in text_lengths] if ragged_text else [T] * n))
         cl = (C.c_int32 * n)(*([M] * n))
         self._check(self.lib.tts_ar_forward_latents(self.handle, _ptr(lat), _ptr(txt), max(T, 1), tl, _ptr(codes), max(M, 1),
                                                     cl, n, _ptr(out), self._stream()), "tts_ar_forward_latents")
