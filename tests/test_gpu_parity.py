@@ -211,9 +211,9 @@ def make_small(b200, layers=2, U=2, T=12, attn_std=0.04, **kw):
 
 
 def kv_rows(m, layer, page, kv, head, n_pages):
-    """Python restatement of layout.h kv_row_offset: pool[layer][page][kv][head][slot 32][64] bf16."""
+    """Python restatement of layout.h kv_row_offset: pool[layer][head][page][kv][slot 32][64] bf16."""
     pool = m.debug_buffer("kv", ((layer + 1) * n_pages * 2 * 16 * 32 * 64,), dtype=torch.bfloat16)
-    off = ((((layer * n_pages + page) * 2 + kv) * 16 + head) * 32) * 64
+    off = ((((layer * 16 + head) * n_pages + page) * 2 + kv) * 32) * 64
     return pool[off: off + 32 * 64].view(32, 64).float().cpu()
 
 

@@ -102,7 +102,7 @@ __device__ __forceinline__ void attn_unit(const Params& P, int layer, int row, i
     }
     const int run = min(seg_end - p, kPage - s0);
     const __nv_bfloat16* kb = P.kv + kv_row_offset(layer, P.n_pages, page, 0, head, s0) + dc * 8;
-    const __nv_bfloat16* vb = kb + (size_t)kH * kPage * kHD;
+    const __nv_bfloat16* vb = kb + kKvVOffset;
     uint4 kf[8], vf[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -226,7 +226,7 @@ static __device__ void attn_tile16(const Params& P, int layer, int r0, int nq, i
   for (int c0 = 0; c0 < kv_len; c0 += 16) {
     const int page = pt[c0 >> 5];
     const __nv_bfloat16* kb_ = P.kv + kv_row_offset(layer, P.n_pages, page, 0, head, c0 & 31);
-    const __nv_bfloat16* vb_ = kb_ + (size_t)kH * kPage * kHD;
+    const __nv_bfloat16* vb_ = kb_ + kKvVOffset;
     // K: B fragments of the two position n-tiles; V: B fragments of the eight dim n-tiles (issued together)
     uint32_t kf[2][4][2];
 #pragma unroll

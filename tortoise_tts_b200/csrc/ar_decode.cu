@@ -162,9 +162,7 @@ __device__ __forceinline__ void build_rinfo(const Params& P, int tile_row0, int 
 
 // Pull the NEXT layer's K/V pages of this CTA's attention rows and its small fp32 parameters into L2 (bulk prefetch), so
 // the attention phase and the LayerNorm / bias loads are not HBM stalls.  Called by `nthr` threads (index t).
-template <int MODE>
-__device__ __forceinline__ void prefetch_next(const Params& P, const Smem& sm, int head, int pf_layer, int t, int nthr) {
-  using C = DecCfg<MODE>;
+__device__ __forceinline__ void prefetch_next(const Params& P, const Smem& sm, int head, int pf_layer, int attn_rows, int t, int nthr) {
   if (pf_layer < 0 || pf_layer > P.n_layers) return;
   // the small fp32 parameters (LN gains/biases, GEMM biases: one contiguous block per layer, tts_ar.cu) are
   // read once per step and do not survive 1.3 GB of streaming in L2: pull the next block in, 1/128 per CTA
@@ -178,16 +176,19 @@ __device__ __forceinline__ void prefetch_next(const Params& P, const Smem& sm, i
     }
   }
   if (pf_layer >= P.n_layers) return;
+  // One thread per (attention row, K|V, page).  Same-box A/B at 16 rows (profiles/r02_ab_kv_prefetch.log): per-page
+  // prefetches 654.9 us/step, one merged prefetch per segment (the pool is head-major: a segment is one contiguous range)
+  // 659.7, none 662.3; at 64 rows the prefetch LOSES (1526 vs 1461 us/step without: a layer's K/V is 70+ MB there, two
+  // layers do not fit L2 next to the weight stream), so MODE 4 skips it (the caller).
   const int* ri = rinfo_ptr(sm);
-  const size_t page_stride = (size_t)2 * kH * kPage * kHD;
-  for (int idx = t; idx < C::kAttnRows * 64; idx += nthr) {
+  for (int idx = t; idx < attn_rows * 64; idx += nthr) {
     const int j = idx >> 6, i = idx & 63, pg = i >> 1, kv = i & 1;
     const int len = ri[64 + j], plen = ri[72 + j];
     if (len <= 0) continue;
     const int* pt = ri + 80 + 64 * j;
     const __nv_bfloat16* base = P.kv + kv_row_offset(pf_layer, P.n_pages, 0, kv, head, 0);
-    if (pg * kPage < plen) bulk_prefetch_l2(base + (size_t)pt[pg] * page_stride, kPage * kHD * 2);
-    if (pg * kPage < len - plen) bulk_prefetch_l2(base + (size_t)pt[32 + pg] * page_stride, kPage * kHD * 2);
+    if (pg * kPage < plen) bulk_prefetch_l2(base + (size_t)pt[pg] * kKvPageStride, kPage * kHD * 2);
+    if (pg * kPage < len - plen) bulk_prefetch_l2(base + (size_t)pt[32 + pg] * kKvPageStride, kPage * kHD * 2);
   }
 }
 
@@ -259,8 +260,8 @@ __device__ __forceinline__ void gran_load(Gran& G, const __nv_bfloat16* kvb, con
     cnt = min(16, len - plen - pos0);
     page = pt[32 + (pos0 >> 5)];
   }
-  const __nv_bfloat16* kb = kvb + (size_t)page * (2 * kH * kPage * kHD) + (pos0 & 31) * kHD;
-  const __nv_bfloat16* vb = kb + (size_t)kH * kPage * kHD;
+  const __nv_bfloat16* kb = kvb + (size_t)page * kKvPageStride + (pos0 & 31) * kHD;
+  const __nv_bfloat16* vb = kb + kKvVOffset;
   G.cnt = cnt;
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
@@ -820,26 +821,26 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       prof_mark(P, c, 200 + (is_head ? OP_HEAD : OP_LN_QKV));
       if (layer == 0 && ld_cg_i(P.n_active) == 0) { alive = false; break; }
       {
-        // row facts of the step (layer 0) and the L2 prefetch of the next layer's K/V pages and small parameters: by the
-        // warps the LayerNorm leaves idle (4 rows per CTA: warps 4..7), or by everyone before it (8 rows per CTA)
+        // row facts of the step (layer 0) and the L2 prefetch of the next layer's K/V segments and small parameters (a handful
+        // of bulk-prefetch instructions): by the warps the LayerNorm leaves idle (4 rows per CTA: warps 4..7), else by
+        // everyone (row facts before the LayerNorm, prefetch after its stores)
         const int pf_layer = is_head ? 0 : layer + 1;
         const int ln_warps = is_head ? kNpcB : kNpcA;
-        if (kNpcA == 8) {                // MODE 4: every warp normalises in phase A
-          if (layer == 0) {
-            build_rinfo<MODE>(P, tile_row0, attn_row0, sm, threadIdx.x, kDecThreads);
-            consumer_sync();
+        const bool side = ln_warps <= 4;
+        if (side) {
+          if (threadIdx.x >= 128) {
+            if (layer == 0) {
+              build_rinfo<MODE>(P, tile_row0, attn_row0, sm, threadIdx.x - 128, 128);
+              asm volatile("bar.sync 2, 128;" ::: "memory");
+            }
+            if (MODE != 4) prefetch_next(P, sm, head, pf_layer, C::kAttnRows, threadIdx.x - 128, 128);
           }
-          prefetch_next<MODE>(P, sm, head, pf_layer, threadIdx.x, kDecThreads);
-        } else if (ln_warps == 8) {      // MODE 2 head: all 8 warps normalise (layer != 0); the prefetch goes first
-          prefetch_next<MODE>(P, sm, head, pf_layer, threadIdx.x, kDecThreads);
-        } else if (threadIdx.x >= 128) {
-          if (layer == 0) {
-            build_rinfo<MODE>(P, tile_row0, attn_row0, sm, threadIdx.x - 128, 128);
-            asm volatile("bar.sync 2, 128;" ::: "memory");
-          }
-          prefetch_next<MODE>(P, sm, head, pf_layer, threadIdx.x - 128, 128);
+        } else if (layer == 0) {
+          build_rinfo<MODE>(P, tile_row0, attn_row0, sm, threadIdx.x, kDecThreads);
+          consumer_sync();
         }
         ln_cluster(P, sm, false, sm.red, is_head, rank, is_head ? 0 : tile_row0, ln_warps);
+        if (!side && MODE != 4) prefetch_next(P, sm, head, pf_layer, C::kAttnRows, threadIdx.x, kDecThreads);
       }
       cluster_barrier();
       prof_mark(P, c, 1);

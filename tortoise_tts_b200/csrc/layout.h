@@ -64,10 +64,14 @@ TTS_HD int64_t afrag_elem_offset(int row, int col, int K) {
   return (((int64_t)mt * (K >> 4) + kb) * 32 + lane) * 8 + reg * 2 + (kk & 1);
 }
 
-// ---- KV page pool -----------------------------------------------------------------------------------
-// pool[layer][page][kv (0=K,1=V)][head][slot (32)][64] bf16.  Returns the bf16 element offset of [..][0].
+// ---- KV page pool -----------------------------------------------------------------------------------------------------
+// pool[layer][head][page][kv (0=K,1=V)][slot (32)][64] bf16.  Returns the bf16 element offset of [..][0].
+// Head-major: the K and V blocks of one (head, page) are adjacent (8 KiB), and consecutive pages of a sequence (the host
+// allocates them consecutively) are one contiguous byte range per head -- one bulk L2 prefetch covers a whole segment.
+constexpr int kKvVOffset = kPage * kHD;            // elements from a page's K block to its V block
+constexpr int kKvPageStride = 2 * kPage * kHD;     // elements between consecutive pages of one (layer, head)
 TTS_HD int64_t kv_row_offset(int layer, int n_pages, int page, int kv, int head, int slot) {
-  return (((((int64_t)layer * n_pages + page) * 2 + kv) * kH + head) * kPage + slot) * kHD;
+  return (((((int64_t)layer * kH + head) * n_pages + page) * 2 + kv) * kPage + slot) * kHD;
 }
 
 // ---- static tile schedule ---------------------------------------------------------------------------
