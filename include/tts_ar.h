@@ -154,6 +154,19 @@ int tts_ar_generate(TtsArHandle* h, const TtsArSampling* s, int32_t max_new, int
 int tts_ar_step(TtsArHandle* h, const TtsArSampling* s, int32_t n_steps, int64_t* out_codes,
                 float* out_latents, const int32_t* forced, int32_t* out_choice, void* stream);
 
+/* Streaming hand-off (reference get_generator -> sample_stream yields (next_tokens, final_norm(hidden)) per
+ * step, stream_generator.py:1172, consumed by the HiFiGAN branch of inference.py:266-329): ONE persistent launch runs the whole
+ * sample loop on `stream` and publishes every step through a flag ring in mapped pinned host memory; the host polls the flag and
+ * then reads column `step` of the DEVICE buffers -- no per-chunk launches, allocations or stream synchronisation.
+ *   tts_ar_stream_begin  after tts_ar_prefill, <= 64 sequences; buffers as tts_ar_generate (out_latents required).  ASYNC.
+ *   tts_ar_stream_poll   waits (busy-poll, timeout_us < 0: forever) until (token, latent) of `step` of EVERY sequence are written:
+ *                        1 = ready, 0 = time-out, 2 = the loop ended before this step (all sequences finished / max_new reached).
+ *   tts_ar_stream_end    waits for the launch and reports like tts_ar_sync_result.  SYNC.
+ * Pass a stream of your own (not the one the consumer of the tokens enqueues work on): the launch occupies it until the loop ends. */
+int tts_ar_stream_begin(TtsArHandle* h, const TtsArSampling* s, int32_t max_new, int64_t* out_codes, float* out_latents, void* stream);
+int tts_ar_stream_poll(TtsArHandle* h, int32_t step, int32_t timeout_us);
+int tts_ar_stream_end(TtsArHandle* h, TtsArStats* out, void* stream);
+
 /* Parity hook: the logits the NEXT sample would use.  out dev float32 [rows, n_mel_codes];
  * rows = n_utt right after prefill, n_seq after any step.  *rows_out is written on return. */
 int tts_ar_logits_debug(TtsArHandle* h, float* out, int32_t* rows_out, void* stream);

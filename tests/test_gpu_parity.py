@@ -439,6 +439,14 @@ def test_streaming_generator_matches_batch_path(b200):
                                      return_latents=True, **kw)
     assert torch.equal(toks, whole.cpu())
     assert torch.equal(torch.stack(lts, 1), lats.cpu())
+    # stop tokens end the stream early (rows pad with the stop token until the last one has finished, Q7), an abandoned
+    # generator releases the stream, and a second stream on the same handle works
+    g = m.get_generator(ids, max_length=16 + 20, num_return_sequences=2, **kw)
+    first = next(g)
+    assert torch.equal(first[0].cpu(), whole[:, 0].cpu())
+    g.close()
+    toks2 = torch.stack([t.cpu() for t, _ in m.get_generator(ids, max_length=16 + 6, num_return_sequences=2, **kw)], 1)
+    assert torch.equal(toks2, whole[:, :6].cpu())
     m.close()
 
 

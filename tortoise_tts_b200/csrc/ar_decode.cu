@@ -936,7 +936,13 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
     if (c->abort_flag) alive = false;
   }
   consumer_sync();
-  if (threadIdx.x == 0 && blockIdx.x == 0) *P.steps_done = steps_done;
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    *P.steps_done = steps_done;
+    if (P.stream_done) {         // streaming: the launch has ended after steps_done steps (every flag of those steps was published before)
+      __threadfence_system();
+      *reinterpret_cast<volatile int*>(P.stream_done) = steps_done + 1;
+    }
+  }
   if (threadIdx.x == 0) {
     // never leave the kernel with bulk copies still landing in this CTA's shared memory
     for (uint32_t k = pipe.ci; k < fd.f.issued; ++k)

@@ -123,6 +123,10 @@ struct Params {
   int* out_choice;       // nullable [seqs][out_stride]
   float* latent_out;     // OP_LATENT destination rows [n][1024] via latent_dst
   const int* latent_dst; // [rows] destination row index in latent_out or -1
+  // streaming hand-off (tts_ar_stream_begin): mapped pinned host memory; flags[step] counts the sequences whose (token, latent) of
+  // that step are in out_codes / out_latents, done = steps run + 1 once the launch has ended
+  int* stream_flags;
+  int* stream_done;
   // control
   unsigned int* bar_counter;
   int* watchdog;

@@ -444,7 +444,16 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
 }
 
 static __device__ void sample_stage(const Params& P, const Instr& ins, const Smem& sm, int step_col) {
-  for (int seq = blockIdx.x; seq < P.n_seqs; seq += P.G) sample_row(P, sm, seq, step_col);
+  for (int seq = blockIdx.x; seq < P.n_seqs; seq += P.G) {
+    sample_row(P, sm, seq, step_col);
+    if (P.stream_flags) {        // streaming: publish "this sequence's (token, latent) of step step_col is written" to the host
+      consumer_sync();           // every thread's latent stores precede the fence below (CTA barrier + cumulativity)
+      if (threadIdx.x == 0) {
+        __threadfence_system();
+        atomicAdd_system(P.stream_flags + step_col, 1);
+      }
+    }
+  }
 }
 
 }  // namespace tts

@@ -146,6 +146,10 @@ static int create_impl(TtsArHandle* h) {
                                     (size_t)c.max_seqs * (kMaxPagesPerSeg + 2)) + 4096;
   TTS_CUDA(h, cudaMallocHost(&h->h_staging, h->staging_bytes));
   TTS_CUDA(h, cudaEventCreateWithFlags(&h->ev_staging, cudaEventDisableTiming));
+  h->stream_cap = c.max_new_tokens + 8;     // [0]: done flag, [1 + step]: per-step counters
+  TTS_CUDA(h, cudaHostAlloc(&h->h_stream_flags, sizeof(int) * (h->stream_cap + 1), cudaHostAllocMapped));
+  TTS_CUDA(h, cudaHostGetDevicePointer(&h->d_stream_flags, h->h_stream_flags, 0));
+  memset(h->h_stream_flags, 0, sizeof(int) * (h->stream_cap + 1));
   TTS_CUDA(h, cudaMallocHost(&h->h_pinned_codes, sizeof(long long) * (size_t)c.max_seqs * std::max(c.max_new_tokens, 1)));
   TTS_CUDA(h, cudaMallocHost(&h->h_pinned_latent, sizeof(float) * (size_t)c.max_utts * kD));
   TTS_CUDA(h, cudaMallocHost(&h->h_pinned_text, sizeof(int) * (size_t)c.max_utts * std::max(c.max_text_len, 1)));
@@ -207,6 +211,7 @@ extern "C" void tts_ar_destroy(TtsArHandle* h) {
   if (h->h_pinned_latent) cudaFreeHost(h->h_pinned_latent);
   if (h->h_pinned_text) cudaFreeHost(h->h_pinned_text);
   if (h->h_staging) cudaFreeHost(h->h_staging);
+  if (h->h_stream_flags) cudaFreeHost(h->h_stream_flags);
   if (h->ev_staging) cudaEventDestroy(h->ev_staging);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);

@@ -88,6 +88,11 @@ struct TtsArHandle {
   size_t staging_bytes = 0;
   cudaEvent_t ev_staging = nullptr;
   bool staging_busy = false;
+  // streaming hand-off: mapped pinned flags (host pointer / device alias), tts_ar_stream_begin
+  int* h_stream_flags = nullptr;
+  int* d_stream_flags = nullptr;
+  int stream_cap = 0, stream_steps = 0;
+  bool streaming = false;
   // explicit options (tts_ar_set_option)
   int opt_decode_interp = 0, opt_dense_interp = 0, opt_attn_tiles = 0, opt_no_coop = 0;
 

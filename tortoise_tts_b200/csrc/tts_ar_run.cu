@@ -3,6 +3,7 @@
 #include <cstring>
 #include <cstdlib>
 #include <algorithm>
+#include <chrono>
 #include "tts_ar_host.h"
 
 using namespace tts;
@@ -226,7 +227,7 @@ extern "C" int tts_ar_prefill(TtsArHandle* h, const float* latent, const int32_t
 }
 
 static int run_steps(TtsArHandle* h, const TtsArSampling* s, int n_steps, bool skip_last_model, long long* out_codes,
-                     float* out_latents, const int32_t* forced, int32_t* out_choice, cudaStream_t st) {
+                     float* out_latents, const int32_t* forced, int32_t* out_choice, cudaStream_t st, bool streaming = false) {
   const TtsArConfig& c = h->cfg;
   if (!s || s->struct_size != (int)sizeof(TtsArSampling)) return fail(h, TTS_AR_ERR_BAD_ARG, "TtsArSampling.struct_size mismatch");
   if (!out_codes || n_steps < 1) return fail(h, TTS_AR_ERR_BAD_ARG, "bad generate argument");
@@ -258,6 +259,14 @@ static int run_steps(TtsArHandle* h, const TtsArSampling* s, int n_steps, bool s
   const bool cluster = h->use_cluster && !h->opt_decode_interp;
   h->n_groups = cluster ? (h->n_seqs + kDecMaxRows - 1) / kDecMaxRows : 0;
   int rc = 0;
+  if (streaming) {
+    if (h->n_groups != 1) return fail(h, TTS_AR_ERR_CAPACITY, "streaming needs the head-cluster kernel and at most 64 sequences");
+    if (n_steps > h->stream_cap) return fail(h, TTS_AR_ERR_CAPACITY, "stream longer than max_new_tokens");
+    memset(h->h_stream_flags, 0, sizeof(int) * (n_steps + 1));   // the previous stream has ended (tts_ar_stream_begin checks)
+    P.stream_done = h->d_stream_flags;
+    P.stream_flags = h->d_stream_flags + 1;
+    h->stream_steps = n_steps;
+  }
   if (h->n_groups > 1) {
     const int stash = h->logit_rows_cap - (h->cfg.max_utts + 63) / 64 * 64;   // the prompt-pass rows, kept for every group
     if (h->first_step_pending) {
@@ -544,4 +553,40 @@ extern "C" int tts_ar_set_option(TtsArHandle* h, const char* name, int32_t value
     return fail(h, TTS_AR_ERR_BAD_ARG, "unknown option");
   }
   return 0;
+}
+
+// ---- streaming hand-off (reference get_generator / sample_stream yield per step, stream_generator.py:1172) ----
+extern "C" int tts_ar_stream_begin(TtsArHandle* h, const TtsArSampling* s, int32_t max_new, int64_t* out_codes, float* out_latents,
+                                   void* stream) {
+  int rc = check_ready(h, true);
+  if (rc) return rc;
+  if (!h->first_step_pending) return fail(h, TTS_AR_ERR_STATE, "tts_ar_stream_begin needs a fresh tts_ar_prefill");
+  if (h->streaming) return fail(h, TTS_AR_ERR_STATE, "a stream is already open: call tts_ar_stream_end first");
+  if (!out_latents) return fail(h, TTS_AR_ERR_BAD_ARG, "streaming publishes (token, latent) pairs: out_latents is required");
+  rc = run_steps(h, s, max_new, true, (long long*)out_codes, out_latents, nullptr, nullptr, (cudaStream_t)stream, true);
+  if (rc) return rc;
+  h->streaming = true;
+  return 0;
+}
+
+extern "C" int tts_ar_stream_poll(TtsArHandle* h, int32_t step, int32_t timeout_us) {
+  if (!h || !h->streaming) return TTS_AR_ERR_STATE;
+  if (step < 0 || step >= h->stream_steps) return 2;
+  volatile int* f = h->h_stream_flags;
+  const auto t0 = std::chrono::steady_clock::now();
+  for (;;) {
+    if (f[1 + step] >= h->n_seqs) return 1;                         // every sequence's (token, latent) of this step is in the device buffers
+    const int done = f[0];
+    if (done && step >= done - 1) return 2;                          // the launch ended (all sequences finished) before this step
+    if (timeout_us >= 0 &&
+        std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t0).count() > timeout_us)
+      return 0;
+  }
+}
+
+extern "C" int tts_ar_stream_end(TtsArHandle* h, TtsArStats* out, void* stream) {
+  if (!h || !h->streaming) return TTS_AR_ERR_STATE;
+  h->streaming = false;
+  TtsArStats tmp;
+  return tts_ar_sync_result(h, out ? out : &tmp, stream);
 }

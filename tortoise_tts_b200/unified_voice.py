@@ -72,6 +72,10 @@ class UnifiedVoiceB200:
     # ---- lifetime -------------------------------------------------------------------------------------
     def close(self):
         if getattr(self, "handle", None) and self.handle.value:
+            try:
+                self._close_stream()
+            except Exception:
+                pass
             self.lib.tts_ar_destroy(self.handle)
             self.handle = C.c_void_p(0)
 
@@ -298,33 +302,52 @@ class UnifiedVoiceB200:
         embs[:, -1] = self.start_mel_token
         return embs
 
-    def get_generator(self, inputs, max_length=500, chunk=8, **hf_generate_kwargs):
-        """Yields (next_tokens [B] int64, latent [B, 1024]) per step like sample_stream
-        (stream_generator.py:1172).  `max_length` counts the prompt (quirk Q9)."""
+    def get_generator(self, inputs, max_length=500, chunk=None, **hf_generate_kwargs):
+        """Yields (next_tokens [B] int64, latent [B, 1024]) per step like sample_stream (stream_generator.py:1172).
+        `max_length` counts the prompt (quirk Q9).  ONE persistent launch on a side stream runs the whole sample loop and
+        publishes every step through a flag ring in mapped pinned memory (include/tts_ar.h tts_ar_stream_*): per yielded
+        step the host only polls a flag and slices the device buffers -- no launch, allocation or stream synchronisation.
+        (`chunk` is accepted for backward compatibility and ignored.)"""
         if self._embed_state is None:
             raise AssertionError("compute_embeddings must be called first")   # ref: assert cached_mel_emb is not None
         n_cand = int(hf_generate_kwargs.pop("num_return_sequences", 1))
         s = self._sampling(hf_generate_kwargs)
+        self._close_stream()
         latent, text = self._embed_state
         U, _ = self._prefill(latent, text, n_cand)
         B = U * n_cand
         total = int(max_length) - inputs.shape[1]
         total = min(total, self.cfg.max_new_tokens)
-        done = 0
-        while done < total:
-            n = min(chunk, total - done)
-            codes = torch.full((B, n), self.stop_mel_token, dtype=torch.int64, device=self.device)
-            lat = torch.zeros((B, n, self.geometry.model_dim), dtype=torch.float32, device=self.device)
-            last = done + n >= total
-            fn = self.lib.tts_ar_generate if (last and done == 0) else self.lib.tts_ar_step
-            self._check(fn(self.handle, C.byref(s), n, _ptr(codes), _ptr(lat), C.c_void_p(0), C.c_void_p(0), self._stream()),
-                        "tts_ar_step")
-            st = self.sync_stats()
-            for j in range(st.steps_run):
-                yield codes[:, j], lat[:, j]
-            done += n
-            if st.all_finished or st.steps_run < n:
-                return
+        if total < 1:
+            return
+        codes = torch.full((B, total), self.stop_mel_token, dtype=torch.int64, device=self.device)
+        lat = torch.empty((B, total, self.geometry.model_dim), dtype=torch.float32, device=self.device)
+        if getattr(self, "_side_stream", None) is None:
+            self._side_stream = torch.cuda.Stream(device=self.device)
+        side = self._side_stream
+        side.wait_stream(torch.cuda.current_stream(self.device))          # prompt pass and buffer fills precede the loop
+        sp = C.c_void_p(side.cuda_stream)
+        self._check(self.lib.tts_ar_stream_begin(self.handle, C.byref(s), total, _ptr(codes), _ptr(lat), sp), "tts_ar_stream_begin")
+        self._open_stream = (sp, codes, lat)
+        try:
+            for k in range(total):
+                r = self.lib.tts_ar_stream_poll(self.handle, k, -1)
+                if r < 0:
+                    self._check(r, "tts_ar_stream_poll")
+                if r == 2:
+                    break
+                yield codes[:, k], lat[:, k]
+        finally:
+            self._close_stream()
+
+    def _close_stream(self):
+        st = getattr(self, "_open_stream", None)
+        if st is None:
+            return
+        self._open_stream = None
+        stats = _lib.TtsArStats()
+        self._check(self.lib.tts_ar_stream_end(self.handle, C.byref(stats), st[0]), "tts_ar_stream_end")
+        self.last_stats = stats
 
     def forward(self, speech_conditioning_latent, text_inputs, text_lengths, mel_codes, wav_lengths, types=None,
                 text_first=True, raw_mels=None, return_attentions=False, return_latent=False, clip_inputs=True, out=None,
