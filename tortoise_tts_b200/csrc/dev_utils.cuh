@@ -164,7 +164,7 @@ __device__ __forceinline__ void red_add_s64(long long* p, long long v) {
 }
 __device__ __forceinline__ longlong2 ld_cg_ll2(const void* p) { return __ldcg(reinterpret_cast<const longlong2*>(p)); }
 
-// ---- tensor core (legacy warp-level path; the dense contractions use tcgen05, see gemm_tc.cu) -----------
+// ---- tensor core, warp-level path of the HBM-bound decode GEMMs (the dense contractions use tcgen05: tc_gemm.cuh) ----
 __device__ __forceinline__ void ldmatrix_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
                : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
@@ -198,7 +198,7 @@ __device__ __forceinline__ float warp_max(float v) {
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
 }
-// 512 consumer threads; `scratch` = 32 floats of shared memory.  All consumer threads must call.
+// kConsumerThreads (256) consumer threads; `scratch` = 32 floats of shared memory.  All consumer threads must call.
 __device__ __forceinline__ float block_sum(float v, float* scratch) {
   int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   v = warp_sum(v);
