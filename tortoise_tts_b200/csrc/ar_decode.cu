@@ -197,9 +197,19 @@ __device__ __forceinline__ void prefetch_next(const Params& P, const Smem& sm, i
 // memory, so the rows are read from L2 once per cluster instead of once per CTA.  The caller follows with cluster_barrier().
 // `gb` = the staged (gain, bias) vectors: one pair, or two for the head (ln_f then final_norm, `dbl`); the head is the
 // same call site as ln_1 on purpose -- code that runs once per step is fetched cold, code shared with the layers is not.
-// `fixed`: the source is the fixed-point accumulator y (ln_2) instead of x.
-__device__ __forceinline__ void ln_cluster(const Params& P, const Smem& sm, bool fixed, const float* gb, bool dbl, int rank, int rbase,
-                                           int npc) {
+// Source of the rows (`src`):
+//   LN_SRC_X    plain fp32 x, complete behind a grid barrier (layer 0: written by the sampler)
+//   LN_SRC_XT   the tagged residual stream xt (layers >= 1 and the head): written by the mlp.c_proj owners of the previous
+//               block as (value, tag) pairs; the warp POLLS its row until every element carries `expect` (the block's tag) --
+//               this replaces the grid barrier between mlp.c_proj and ln_1
+//   LN_SRC_Y    the counting accumulator y (ln_2): polled until every word has received `expect` contributions (residual
+//               + 16 heads) -- this replaces the grid barrier between the attention block and ln_2
+// Polling reads one 16-byte piece per lane until it is complete, then the whole row once, and re-reads the row only if a
+// piece is still incomplete (contributions land in any order).  Every wait is watchdogged.
+enum LnSrc : int { LN_SRC_X = 0, LN_SRC_XT = 1, LN_SRC_Y = 2 };
+
+__device__ __forceinline__ void ln_cluster(const Params& P, const Smem& sm, int src, uint32_t expect, const float* gb, bool dbl, int rank,
+                                           int rbase, int npc) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   if (w >= npc) return;
   const int r = npc * rank + w;
@@ -207,12 +217,44 @@ __device__ __forceinline__ void ln_cluster(const Params& P, const Smem& sm, bool
   const bool ok = grow < P.n_rows;
   const int lrow = ok ? grow : 0;
   float4 v[8];
-  if (fixed) {
+  if (src == LN_SRC_Y) {
     const long long* yp = P.y + (size_t)lrow * kD;
+    const long long t0 = clock64();
+    for (;;) {
+      const longlong2 p0 = ld_relaxed_ll2(yp + 4 * lane);
+      if (__all_sync(0xffffffffu, cnt_count(p0.x) == (int)expect && cnt_count(p0.y) == (int)expect)) break;
+      if (clock64() - t0 > kWatchdogCycles || sm.ctrl->abort_flag) { sm.ctrl->abort_flag = 1; *reinterpret_cast<volatile int*>(P.watchdog) = 1; break; }
+    }
+    for (;;) {
+      bool good = true;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const longlong2 a = ld_cg_ll2(yp + 128 * j + 4 * lane), b = ld_cg_ll2(yp + 128 * j + 4 * lane + 2);
-      v[j] = make_float4(from_fixed(a.x), from_fixed(a.y), from_fixed(b.x), from_fixed(b.y));
+      for (int j = 0; j < 8; ++j) {
+        const longlong2 a = ld_relaxed_ll2(yp + 128 * j + 4 * lane), b = ld_relaxed_ll2(yp + 128 * j + 4 * lane + 2);
+        good = good && cnt_count(a.x) == (int)expect && cnt_count(a.y) == (int)expect && cnt_count(b.x) == (int)expect &&
+               cnt_count(b.y) == (int)expect;
+        v[j] = make_float4(cnt_value(a.x), cnt_value(a.y), cnt_value(b.x), cnt_value(b.y));
+      }
+      if (__all_sync(0xffffffffu, good)) break;
+      if (clock64() - t0 > kWatchdogCycles || sm.ctrl->abort_flag) { sm.ctrl->abort_flag = 1; *reinterpret_cast<volatile int*>(P.watchdog) = 1; break; }
+    }
+  } else if (src == LN_SRC_XT) {
+    const uint2* xp = P.xt + (size_t)lrow * kD;
+    const long long t0 = clock64();
+    for (;;) {
+      const uint4 p0 = ld_relaxed_u4(xp + 2 * lane);
+      if (__all_sync(0xffffffffu, p0.y == expect && p0.w == expect)) break;
+      if (clock64() - t0 > kWatchdogCycles || sm.ctrl->abort_flag) { sm.ctrl->abort_flag = 1; *reinterpret_cast<volatile int*>(P.watchdog) = 1; break; }
+    }
+    for (;;) {
+      bool good = true;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const uint4 a = ld_relaxed_u4(xp + 128 * j + 4 * lane), b = ld_relaxed_u4(xp + 128 * j + 4 * lane + 2);
+        good = good && a.y == expect && a.w == expect && b.y == expect && b.w == expect;
+        v[j] = make_float4(__uint_as_float(a.x), __uint_as_float(a.z), __uint_as_float(b.x), __uint_as_float(b.z));
+      }
+      if (__all_sync(0xffffffffu, good)) break;
+      if (clock64() - t0 > kWatchdogCycles || sm.ctrl->abort_flag) { sm.ctrl->abort_flag = 1; *reinterpret_cast<volatile int*>(P.watchdog) = 1; break; }
     }
   } else {
     const float* xp = P.x + (size_t)lrow * kD;
@@ -600,20 +642,20 @@ __device__ void proj_splitk(const Params& P, int rank, int row_lo, int tile_row0
 #pragma unroll
         for (int tt = 0; tt < 2; ++tt) {
           long long* yp = P.y + (size_t)row * kD + col0 + 8 * tt;
-          red_add_s64(yp, to_fixed(acc[mt][tt][2 * hh]));
-          red_add_s64(yp + 1, to_fixed(acc[mt][tt][2 * hh + 1]));
+          red_add_s64(yp, cnt_contrib(acc[mt][tt][2 * hh]));          // value and contribution count in one atomic
+          red_add_s64(yp + 1, cnt_contrib(acc[mt][tt][2 * hh + 1]));
         }
       }
   }
 }
 
-// ---- mlp.c_proj of row group `grp`: x = y + h . W + bias ; y = x + next layer's attn.c_proj bias -----------------------
+// ---- mlp.c_proj of row group `grp`: xt = (y + h . W + bias, tag) ; y = x + next layer's attn.c_proj bias, count 1 --------
 // A cluster owns 4 n8-tiles (32 output columns); CTA rank r multiplies the K range [1024r, 1024r+1024) of h with the 4
 // tiles (4 streamed chunks), so it reads only its quarter of h (32 KiB of bf16 A fragments per m-tile from L2 instead of
 // 128 KiB: the SM's ~55 GB/s L2 read port is what this stage waits for).  The four K-partials of a tile are sent to the
 // tile's owner (rank t owns tile t) through distributed shared memory and summed there in rank order (deterministic).
 template <int MODE>
-__device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pipe, Feeder& fd, int rank, int grp, bool commit) {
+__device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pipe, Feeder& fd, int rank, int grp, bool commit, uint32_t xtag) {
   using C = DecCfg<MODE>;
   constexpr int MT = C::kMtB;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -693,10 +735,15 @@ __device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pi
       s0 += v.x;
       s1 += v.y;
     }
-    const float x0 = from_fixed(old.x) + s0 + bias.x, x1 = from_fixed(old.y) + s1 + bias.y;
-    *reinterpret_cast<float2*>(P.x + (size_t)erow * kD + col) = make_float2(x0, x1);
-    // the next layer's attention block accumulates onto residual + attn.c_proj bias
-    *reinterpret_cast<longlong2*>(P.y + (size_t)erow * kD + col) = make_longlong2(to_fixed(x0 + nbias.x), to_fixed(x1 + nbias.y));
+    const float x0 = cnt_value(old.x) + s0 + bias.x, x1 = cnt_value(old.y) + s1 + bias.y;
+    // the residual stream for the next block, self-validating: (value, tag) pairs polled by its ln_1 (no grid barrier)
+    st_tagged2(P.xt + (size_t)erow * kD + col, x0, x1, xtag);
+    // the next layer's attention block accumulates onto residual + attn.c_proj bias, contribution count 1.  Written as an
+    // atomic ADD of (target - what was read): it commutes with the next block's head contributions, so no ordering between
+    // this CTA and the clusters that are already ahead is needed.
+    long long* yp = P.y + (size_t)erow * kD + col;
+    red_add_s64(yp, cnt_word(x0 + nbias.x, 1) - old.x);
+    red_add_s64(yp + 1, cnt_word(x1 + nbias.y, 1) - old.y);
   }
 }
 
@@ -754,6 +801,27 @@ __device__ __forceinline__ bool dec_grid_barrier(const Params& P, const Smem& sm
   }
   consumer_sync();
   if (rec) P.prof[8192 + blockIdx.x * 8 + prof_slot + 3] = globaltimer_ns();
+  return c->abort_flag == 0;
+}
+
+// ---- phase boundary WITHOUT a grid barrier: the next stage polls its (self-validating) input itself ------------------
+// What is left of the barrier is CTA-local: every warp is done with the previous stage's ring slots and reduction buffer,
+// warp 0 refills the ring, warps 4..7 stage the next LayerNorm's gains / biases.
+__device__ __forceinline__ bool dec_soft_boundary(const Params& P, const Smem& sm, Feeder& fd, int extra, const float* stage, int nstage,
+                                                  int stage_off) {
+  Ctrl* c = sm.ctrl;
+  consumer_sync();
+  fd.pending += extra;
+  const int refill_n = min(fd.pending, 6);
+  fd.pending -= refill_n;
+  if (threadIdx.x < 32 && refill_n) feed(P, c, sm.ring, fd.f, refill_n, fd.head, fd.rank, fd.ht0, fd.hcnt);
+  if (threadIdx.x >= 128 && nstage) {
+    const int t = threadIdx.x - 128;
+#pragma unroll 1
+    for (int k = t; k < nstage * (kD / 4); k += 128) cp_async_cg16(sm.red + stage_off + 4 * k, stage + 4 * k);
+    cp_async_wait_all();
+  }
+  consumer_sync();
   return c->abort_flag == 0;
 }
 
@@ -815,8 +883,14 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       // ---- phase A: ln_1 -> q,k,v of this head -> attention -> split-K c_proj -> y ----
       prof_mark(P, c, 100 + (is_head ? OP_HEAD : OP_LN_QKV));
       const int pslot = (step == P.prof_step && layer == 3) ? 0 : -4;
-      // gains / biases to stage: ln_1 (g, b), or lnf_g, lnf_b, fn_g, fn_b (contiguous, tts_ar.cu) for the head
-      alive = dec_grid_barrier(P, sm, epoch, fd, 0, pslot, is_head ? P.lnf_g : layer_f(P, layer) + kFOffLn1g, is_head ? 4 : 2);
+      // gains / biases to stage: ln_1 (g, b), or lnf_g, lnf_b, fn_g, fn_b (contiguous, tts_ar.cu) for the head.
+      // Layer 0 follows the sampler (plain x, step bookkeeping): a real grid barrier.  Every later block, and the head, POLLS
+      // the tagged residual stream the previous block's mlp.c_proj owners write (ln_cluster LN_SRC_XT): no grid barrier.
+      const uint32_t xtag = (uint32_t)(step * (P.n_layers + 1) + layer);      // >= 1 for layer >= 1; xt is zeroed per launch
+      if (layer == 0)
+        alive = dec_grid_barrier(P, sm, epoch, fd, 0, pslot, layer_f(P, layer) + kFOffLn1g, 2);
+      else
+        alive = dec_soft_boundary(P, sm, fd, 0, is_head ? P.lnf_g : layer_f(P, layer) + kFOffLn1g, is_head ? 4 : 2, 0);
       if (!alive) break;
       prof_mark(P, c, 200 + (is_head ? OP_HEAD : OP_LN_QKV));
       if (layer == 0 && ld_cg_i(P.n_active) == 0) { alive = false; break; }
@@ -839,7 +913,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
           build_rinfo<MODE>(P, tile_row0, attn_row0, sm, threadIdx.x, kDecThreads);
           consumer_sync();
         }
-        ln_cluster(P, sm, false, sm.red, is_head, rank, is_head ? 0 : tile_row0, ln_warps);
+        ln_cluster(P, sm, layer == 0 ? LN_SRC_X : LN_SRC_XT, xtag, sm.red, is_head, rank, is_head ? 0 : tile_row0, ln_warps);
         if (!side && MODE != 4) prefetch_next(P, sm, head, pf_layer, C::kAttnRows, threadIdx.x, kDecThreads);
       }
       cluster_barrier();
@@ -872,14 +946,15 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       proj_splitk<MODE>(P, rank, row_lo, tile_row0, sm, pipe);
       // ---- phase B: ln_2 -> c_fc -> gelu_new ----
       prof_mark(P, c, 100 + OP_LN_FC);
-      alive = dec_grid_barrier(P, sm, epoch, fd, 2, pslot + 1, layer_f(P, layer) + kFOffLn2g, 2, kStageOffLn2);   // + the two split-K c_proj slots
+      // no grid barrier: ln_2 polls the counting accumulator y until residual + 16 heads have landed (ln_cluster LN_SRC_Y)
+      alive = dec_soft_boundary(P, sm, fd, 2, layer_f(P, layer) + kFOffLn2g, 2, kStageOffLn2);   // + the two split-K c_proj slots
       if (!alive) break;
       prof_mark(P, c, 200 + OP_LN_FC);
 #pragma unroll 1
       for (int grp = 0; grp < C::kGroups; ++grp) {
         if (grp) cluster_barrier();       // every CTA of the cluster has multiplied the previous group's rows
         const int rbase = 16 * C::kMtB * grp;
-        ln_cluster(P, sm, true, sm.red + kStageOffLn2, false, rank, rbase, kNpcB);
+        ln_cluster(P, sm, LN_SRC_Y, 1 + kH, sm.red + kStageOffLn2, false, rank, rbase, kNpcB);
         cluster_barrier();
         prof_mark(P, c, 1);
         const float* bias = layer_f(P, layer) + kFOffBfc;
@@ -898,7 +973,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       if (!alive) break;
       prof_mark(P, c, 200 + OP_PROJ2);
 #pragma unroll 1
-      for (int grp = 0; grp < C::kGroups; ++grp) proj2_stage<MODE>(P, layer, sm, pipe, fd, rank, grp, grp == C::kGroups - 1);
+      for (int grp = 0; grp < C::kGroups; ++grp) proj2_stage<MODE>(P, layer, sm, pipe, fd, rank, grp, grp == C::kGroups - 1, xtag + 1);
       if (c->abort_flag) alive = false;
     }
     if (!alive) break;
@@ -912,7 +987,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
         for (int k = threadIdx.x; k < 4 * (kD / 4); k += kDecThreads) cp_async_cg16(sm.red + 4 * k, P.lnf_g + 4 * k);
         cp_async_wait_all();
         consumer_sync();
-        ln_cluster(P, sm, false, sm.red, true, rank, rbase, kNpcB);
+        ln_cluster(P, sm, LN_SRC_XT, (uint32_t)(step * (P.n_layers + 1) + P.n_layers), sm.red, true, rank, rbase, kNpcB);
         cluster_barrier();
       }
       for (int tb = 0; tb < hcnt; tb += 6) {

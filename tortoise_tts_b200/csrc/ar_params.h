@@ -72,8 +72,9 @@ struct Params {
   // activations (row-indexed)
   float* x;              // [rows][1024] residual stream, fp32
   long long* y;          // cluster decode kernel: [16][1024] residual stream between the attention and MLP blocks,
-                         //   accumulated by the 16 heads with integer atomics in 2^-32 fixed point (order-independent
-                         //   => deterministic); zero outside phases A..C of a layer; nullptr in the interpreter kernel
+                         //   accumulated by the 16 heads with integer atomics as counting fixed-point words (dev_utils.cuh
+                         //   cnt_*: order-independent => deterministic, and self-validating); nullptr in the interpreter kernel
+  uint2* xt;             // cluster decode kernels: [rows][1024] (fp32 bits, tag) -- the residual stream between blocks, self-validating
   float* q;              // [rows][1024] query, pre-scaled by 1/sqrt(64)
   __nv_bfloat16* ctx;    // A-fragment layout, K = 1024
   __nv_bfloat16* hbuf;   // A-fragment layout, K = 4096

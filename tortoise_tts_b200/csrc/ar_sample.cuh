@@ -435,8 +435,8 @@ static __device__ void sample_row(const Params& P, const Smem& sm, int seq, int 
     if (b4) {
       const float4 bb = b4[i];
       longlong2* y2 = reinterpret_cast<longlong2*>(P.y + (size_t)seq * kD + 4 * i);
-      y2[0] = make_longlong2(to_fixed(xv.x + bb.x), to_fixed(xv.y + bb.y));
-      y2[1] = make_longlong2(to_fixed(xv.z + bb.z), to_fixed(xv.w + bb.w));
+      y2[0] = make_longlong2(cnt_word(xv.x + bb.x, 1), cnt_word(xv.y + bb.y, 1));   // counting accumulator: 1 contribution so far
+      y2[1] = make_longlong2(cnt_word(xv.z + bb.z, 1), cnt_word(xv.w + bb.w, 1));
     }
   }
   consumer_sync();   // sc / ev / scratch are reused by the next row

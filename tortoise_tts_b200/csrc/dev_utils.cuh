@@ -164,6 +164,32 @@ __device__ __forceinline__ void red_add_s64(long long* p, long long v) {
 }
 __device__ __forceinline__ longlong2 ld_cg_ll2(const void* p) { return __ldcg(reinterpret_cast<const longlong2*>(p)); }
 
+// ---- self-validating data (head-cluster decode kernels: two of the three grid barriers of a block are replaced by polling
+// the data itself; ar_decode.cu) ------------------------------------------------------------------------------------------
+// Counting accumulator: a 64-bit word = (2^-24 fixed-point value << 8) | count.  Every contribution is one red.add of
+// (value << 8) + 1, so value and count change together, atomically, in L2: a reader that sees count == expected sees the
+// complete sum -- no flag, no fence, no barrier.  Integer adds commute => the sum is still order-independent (deterministic).
+constexpr float kCntScale = 16777216.0f, kCntInv = 1.0f / 16777216.0f;
+__device__ __forceinline__ long long cnt_contrib(float v) { return (__float2ll_rn(v * kCntScale) << 8) + 1ll; }
+__device__ __forceinline__ long long cnt_word(float v, int count) { return (__float2ll_rn(v * kCntScale) << 8) | (long long)count; }
+__device__ __forceinline__ float cnt_value(long long w) { return __ll2float_rn(w >> 8) * kCntInv; }
+__device__ __forceinline__ int cnt_count(long long w) { return (int)(w & 0xff); }
+// strong (relaxed, gpu scope) 16-byte loads for polling: never cached in L1, single-copy atomic per 8-byte half
+__device__ __forceinline__ longlong2 ld_relaxed_ll2(const void* p) {
+  longlong2 v;
+  asm volatile("ld.relaxed.gpu.global.v2.s64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 ld_relaxed_u4(const void* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+// tagged fp32 pair (value, tag, value, tag): one 16-byte store, each (value, tag) half lands atomically
+__device__ __forceinline__ void st_tagged2(void* p, float v0, float v1, uint32_t tag) {
+  asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(__float_as_uint(v0)), "r"(tag), "r"(__float_as_uint(v1)), "r"(tag) : "memory");
+}
+
 // ---- tensor core, warp-level path of the HBM-bound decode GEMMs (the dense contractions use tcgen05: tc_gemm.cuh) ----
 __device__ __forceinline__ void ldmatrix_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"

@@ -108,6 +108,7 @@ static int create_impl(TtsArHandle* h) {
   DALLOC(h, h->d_x, (size_t)h->rows_cap * kD);
   DALLOC(h, h->d_q, (size_t)h->rows_cap * kD);
   DALLOC(h, h->d_y, (size_t)kDecMaxRows * kD);
+  DALLOC(h, h->d_xt, (size_t)kDecMaxRows * kD);
   DALLOC(h, h->d_ctx, (size_t)h->rows_cap * kD);
   DALLOC(h, h->d_xn, (size_t)h->rows_cap * kD);
   DALLOC(h, h->d_h, (size_t)h->rows_cap * kD4);

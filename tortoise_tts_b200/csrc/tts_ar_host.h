@@ -58,7 +58,8 @@ struct TtsArHandle {
   DenseW dense;
 
   // activations / cache (device)
-  long long* d_y = nullptr;            // cluster decode kernel: attention-block accumulator [16][1024]
+  long long* d_y = nullptr;            // cluster decode kernels: attention-block counting accumulator [64][1024]
+  uint2* d_xt = nullptr;               // cluster decode kernels: tagged residual stream between blocks [64][1024]
   bool use_cluster = false;         // 16 clusters of 8 CTAs can be co-resident (checked at create)
   float *d_x = nullptr, *d_q = nullptr, *d_logits = nullptr, *d_cur_latent = nullptr, *d_part = nullptr;
   __nv_bfloat16 *d_ctx = nullptr, *d_h = nullptr, *d_kv = nullptr, *d_xn = nullptr;

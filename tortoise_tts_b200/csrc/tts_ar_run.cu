@@ -57,7 +57,12 @@ static int launch(TtsArHandle* h, Params& P, cudaStream_t st, bool cluster = fal
     P.y = h->d_y;
     P.mt_max = decode_mt_smem(mode);
     P.n_slots = smem_max_slots(P.mt_max, h->smem_budget);
-    TTS_CUDA(h, cudaMemsetAsync(h->d_y, 0, sizeof(long long) * kDecRows * mode * kD, st));
+    // y: counting accumulators, one contribution (the residual) deemed present in rows the sampler does not re-initialise
+    // (finished sequences are still carried through the layers); xt: tags of a previous launch must not validate
+    launch_fill_i64(h->d_y, (size_t)kDecRows * mode * kD, 1ll, st);
+    TTS_CUDA(h, cudaMemsetAsync(h->d_xt, 0, sizeof(uint2) * kDecRows * mode * kD, st));
+    P.xt = h->d_xt;
+    h->launches += 1;
     e = launch_decode(P, mode, smem_total_bytes(P.mt_max, P.n_slots), h->cfg.device, decode_cooperative(h), st);
     if (e != cudaSuccess) return cuda_fail(h, e, "cudaLaunchKernelEx(ar_decode_kernel)");
     h->launches += 1;
