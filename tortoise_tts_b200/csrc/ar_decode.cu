@@ -406,9 +406,14 @@ __device__ void attn_local(const Params& P, int layer, int head, int attn_row0, 
       if (g1 > g0) {
         const int* pt = ri + 80 + 64 * j;
         const __nv_bfloat16* kvb = P.kv + kv_row_offset(layer, P.n_pages, 0, 0, head, 0) + dc * 8;
-        Gran A, B, Cg;                                 // three granules in flight per warp (12 KiB)
-        gran_load(A, kvb, pt, g0, Gp, plen, len, rg);
-        if (g0 + 1 < g1) gran_load(B, kvb, pt, g0 + 1, Gp, plen, len, rg);
+#ifndef TTS_ATTN_DEPTH
+#define TTS_ATTN_DEPTH 3
+#endif
+        constexpr int NG = TTS_ATTN_DEPTH;             // granules in flight per warp (4 KiB each), a register ring
+        Gran G[NG];
+#pragma unroll
+        for (int i = 0; i < NG - 1; ++i)
+          if (g0 + i < g1) gran_load(G[i], kvb, pt, g0 + i, Gp, plen, len, rg);
         float qv[8];
         {
           const float* qp = P.q + (size_t)row * kD + head * kHD + dc * 8;
@@ -417,19 +422,14 @@ __device__ void attn_local(const Params& P, int layer, int head, int attn_row0, 
           qv[4] = b.x * kLog2e; qv[5] = b.y * kLog2e; qv[6] = b.z * kLog2e; qv[7] = b.w * kLog2e;
         }
         int qend = ((q + 1) * Gt) >> 2;               // first granule of the next quarter
-        for (int g = g0; g < g1; g += 3) {
-          if (g + 2 < g1) gran_load(Cg, kvb, pt, g + 2, Gp, plen, len, rg);
-          if (QPW > 1) while (g >= qend) { flush(); qend = ((q + 1) * Gt) >> 2; }
-          gran_reduce(A, qv, rg, m, l, acc);
-          if (g + 1 < g1) {
-            if (g + 3 < g1) gran_load(A, kvb, pt, g + 3, Gp, plen, len, rg);
-            if (QPW > 1) while (g + 1 >= qend) { flush(); qend = ((q + 1) * Gt) >> 2; }
-            gran_reduce(B, qv, rg, m, l, acc);
-          }
-          if (g + 2 < g1) {
-            if (g + 4 < g1) gran_load(B, kvb, pt, g + 4, Gp, plen, len, rg);
-            if (QPW > 1) while (g + 2 >= qend) { flush(); qend = ((q + 1) * Gt) >> 2; }
-            gran_reduce(Cg, qv, rg, m, l, acc);
+        for (int g = g0; g < g1; g += NG) {
+#pragma unroll
+          for (int k = 0; k < NG; ++k) {
+            if (g + k < g1) {
+              if (g + k + NG - 1 < g1) gran_load(G[(k + NG - 1) % NG], kvb, pt, g + k + NG - 1, Gp, plen, len, rg);
+              if (QPW > 1) while (g + k >= qend) { flush(); qend = ((q + 1) * Gt) >> 2; }
+              gran_reduce(G[k], qv, rg, m, l, acc);
+            }
           }
         }
       }
