@@ -207,6 +207,19 @@ int tts_ar_debug_copy(TtsArHandle* h, const char* name, void* dst, uint64_t byte
 int tts_ar_debug_gemm(TtsArHandle* h, const void* a_bf16, const void* wt_bf16, const float* bias, float* out,
                       int32_t M, int32_t N, int32_t K, int32_t bn, void* stream);
 
+/* Allocation-free GEMM.  No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  No handle:
+ * out[M][N] (dev fp32) = bf16(a)[M][K] . wt[N][K]^T + bias[N] on the calling thread's CURRENT device, with the tcgen05
+ * kernel of tts_ar_debug_gemm; `a` is dev fp32 row-major (rounded to bf16, nearest-even, as the dense passes round their
+ * LayerNorm output), wt dev bf16 row-major, both 16-byte aligned, K % 64 == 0, bias nullable, bn = 128 or 256.
+ * The bf16 copy of `a` and the kernel's watchdog word are staged in a static __device__ array of 4 MiB + 256 B that every
+ * GPU loading the library holds until exit: M * K <= 2,097,152 (e.g. 2048 x 1024, 512 x 4096), else TTS_AR_ERR_CAPACITY
+ * (text via tts_ar_last_error(NULL)).  Calls no cudaMalloc / cudaFree / allocating routine.  All calls share the array:
+ * issue them on ONE stream -- calls that overlap on the GPU race on the staged operand.
+ *   status_dev  dev int32 or NULL: receives 0, or 1 if a device-side wait timed out (out is then invalid).  ASYNC. */
+int tts_ar_gemm_f32_noalloc(const float* a_f32, const void* wt_bf16, const float* bias, float* out, int32_t M, int32_t N,
+                            int32_t K, int32_t bn, int32_t* status_dev, void* stream);
+
 /* Explicit per-handle options (all default 0 unless noted); returns TTS_AR_ERR_BAD_ARG for unknown names/values.
  *   "decode_kernel"      0 head-cluster kernels whenever their clusters are co-resident, 1 the interpreter kernel
  *   "dense_kernel"       0 tcgen05 pipeline for the prompt pass / latent re-forward, 1 the interpreter kernel

@@ -14,6 +14,7 @@ SYMBOLS = [
     "tts_ar_prefill", "tts_ar_generate", "tts_ar_step", "tts_ar_logits_debug", "tts_ar_forward_latents",
     "tts_ar_inference_speech_host", "tts_ar_sync_result", "tts_ar_debug_copy", "tts_ar_fixup_codes",
     "tts_ar_debug_gemm", "tts_ar_set_option", "tts_ar_stream_begin", "tts_ar_stream_poll", "tts_ar_stream_end",
+    "tts_ar_gemm_f32_noalloc",
 ]
 
 ABI_VERSION = 2
@@ -83,6 +84,7 @@ def load():
     lib.tts_ar_inference_speech_host.argtypes = [vp, f32p, i32p, i32, C.POINTER(C.c_int32), i32, i32,
                                                  C.POINTER(TtsArSampling), i32, i64p, C.POINTER(C.c_int32), vp]
     lib.tts_ar_debug_gemm.argtypes = [vp, vp, vp, f32p, f32p, i32, i32, i32, i32, vp]
+    lib.tts_ar_gemm_f32_noalloc.argtypes = [f32p, vp, f32p, f32p, i32, i32, i32, i32, i32p, vp]
     lib.tts_ar_set_option.argtypes = [vp, C.c_char_p, i32]
     lib.tts_ar_stream_begin.argtypes = [vp, C.POINTER(TtsArSampling), i32, i64p, f32p, vp]
     lib.tts_ar_stream_poll.argtypes = [vp, i32, i32]

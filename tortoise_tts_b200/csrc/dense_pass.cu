@@ -337,3 +337,105 @@ extern "C" int tts_ar_debug_gemm(TtsArHandle* h, const void* a_bf16, const void*
   h->launches += 1;
   return 0;
 }
+
+// ---- allocation-free GEMM entry point -------------------------------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same tcgen05 kernel as the dense passes and
+// tts_ar_debug_gemm, but the scratch a pass needs -- the bf16 row-major A operand that ln_rows_kernel writes into the
+// cudaMalloc'ed h->d_xn there, and the watchdog word -- lives in a file-scope __device__ array: no handle, no allocation.
+// Every GPU that loads the library holds kNoAllocScratchBytes (4 MiB + 256 B) until exit.  All calls share the array:
+// calls that overlap on one GPU (two streams) race on it; serialise them on one stream.
+namespace tts {
+
+constexpr int kNoAllocHeaderBytes = 256;                        // [0] watchdog word (int), rest reserved
+constexpr long long kNoAllocMaxElems = 2ll * 1024 * 1024;       // M * K <= this many bf16 elements (4 MiB)
+constexpr long long kNoAllocScratchBytes = kNoAllocHeaderBytes + 2 * kNoAllocMaxElems;
+constexpr int kNoAllocMaxDevices = 32;
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress,
+// once per device with that device current.
+static void* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+static int g_noalloc_sms[kNoAllocMaxDevices] = {};
+
+static cudaError_t noalloc_setup(int dev, void** ptr, int* n_sm, bool* is_sm100) {
+  *is_sm100 = true;
+  if (!g_noalloc_ptr[dev]) {
+    int major = 0, sms = 0;
+    cudaError_t e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+    if (e != cudaSuccess) return e;
+    if (major != 10) {
+      *is_sm100 = false;
+      return cudaSuccess;
+    }
+    e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return e;
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess) return e;
+    g_noalloc_sms[dev] = sms;
+    g_noalloc_ptr[dev] = p;
+  }
+  *ptr = g_noalloc_ptr[dev];
+  *n_sm = g_noalloc_sms[dev];
+  return cudaSuccess;
+}
+
+// fp32 activations -> the bf16 A operand in scratch (round to nearest even, as ln_rows_kernel and torch do); clears the
+// watchdog word, which keeps the previous call's value otherwise.
+__global__ void __launch_bounds__(256) noalloc_stage_kernel(const float4* __restrict__ a, uint2* __restrict__ dst, int* hdr, long long n4) {
+  if (blockIdx.x == 0 && threadIdx.x == 0) hdr[0] = 0;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    const float4 v = a[i];
+    dst[i] = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+  }
+}
+
+}  // namespace tts
+
+extern "C" int tts_ar_gemm_f32_noalloc(const float* a_f32, const void* wt_bf16, const float* bias, float* out, int32_t M,
+                                       int32_t N, int32_t K, int32_t bn, int32_t* status_dev, void* stream) {
+  if (!a_f32 || !wt_bf16 || !out) return fail(nullptr, TTS_AR_ERR_BAD_ARG, "gemm_f32_noalloc: null argument");
+  if (M < 1 || N < 1 || K < kTcBK || K % kTcBK || (bn != 128 && bn != 256))
+    return fail(nullptr, TTS_AR_ERR_BAD_ARG, "gemm_f32_noalloc: need M, N >= 1, K a multiple of 64, bn 128 or 256");
+  if ((long long)M * K > kNoAllocMaxElems) {
+    char msg[192];
+    snprintf(msg, sizeof msg, "gemm_f32_noalloc: M * K = %lld exceeds the static scratch of %lld bf16 elements (4 MiB)",
+             (long long)M * K, kNoAllocMaxElems);
+    return fail(nullptr, TTS_AR_ERR_CAPACITY, msg);
+  }
+  if ((reinterpret_cast<uintptr_t>(a_f32) | reinterpret_cast<uintptr_t>(wt_bf16)) & 15)
+    return fail(nullptr, TTS_AR_ERR_BAD_ARG, "gemm_f32_noalloc: a_f32 and wt_bf16 must be 16-byte aligned");
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaGetDevice");
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return fail(nullptr, TTS_AR_ERR_DEVICE, "gemm_f32_noalloc: device ordinal out of range");
+  void* scratch = nullptr;
+  int n_sm = 0;
+  bool is_sm100 = true;
+  e = noalloc_setup(dev, &scratch, &n_sm, &is_sm100);
+  if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaGetSymbolAddress(g_noalloc_scratch)");
+  if (!is_sm100) return fail(nullptr, TTS_AR_ERR_DEVICE, "gemm_f32_noalloc: needs an sm_100 (Blackwell B200) device");
+  int* hdr = reinterpret_cast<int*>(scratch);
+  __nv_bfloat16* a_bf16 = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<unsigned char*>(scratch) + kNoAllocHeaderBytes);
+  CUtensorMap ma, mb;
+  if (!make_map(&ma, a_bf16, M, K, kTcBM) || !make_map(&mb, wt_bf16, N, K, bn))
+    return fail(nullptr, TTS_AR_ERR_CUDA, "gemm_f32_noalloc: cuTensorMapEncodeTiled failed");
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long n4 = (long long)M * K / 4;
+  const int grid = (int)std::max(1ll, std::min((n4 + 255) / 256, (long long)n_sm * 8));
+  noalloc_stage_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4*>(a_f32), reinterpret_cast<uint2*>(a_bf16), hdr, n4);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(nullptr, e, "noalloc_stage_kernel launch");
+  TcGemmArgs g{};
+  g.M = M; g.N = N; g.K = K; g.bias = bias; g.out_f32 = out; g.ldo = N; g.watchdog = hdr;
+  e = (bn == 256) ? launch_tc<256, TC_EPI_STORE>(ma, mb, g, n_sm, st) : launch_tc<128, TC_EPI_STORE>(ma, mb, g, n_sm, st);
+  if (e != cudaSuccess) return cuda_fail(nullptr, e, "tc_gemm_kernel launch");
+  if (status_dev) {
+    e = cudaMemcpyAsync(status_dev, hdr, sizeof(int), cudaMemcpyDeviceToDevice, st);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaMemcpyAsync(status)");
+  }
+  return 0;
+}
