@@ -131,3 +131,27 @@ def ref_generate(m, latent, text, n_cand=1, max_new=8, do_sample=False, temperat
             im.text_pos_embedding.get_fixed_embedding = orig
         return dict(codes=torch.stack(codes, 1), logits=torch.stack(keep) if keep else None,
                     latents=torch.stack(lats, 1), pos_trace=[0] + pos_trace, prefix_len=P1 - 1)
+
+
+def load_reference_clvp():
+    """The reference's CLVP class (tortoise_tts/models/clvp.py).  Its module imports the non-xformers Transformer, which needs
+    `rotary_embedding_torch` (absent here, never called with use_xformers=True): stubbed."""
+    load_reference()
+    if "rotary_embedding_torch" not in sys.modules:
+        m = types.ModuleType("rotary_embedding_torch")
+        m.__spec__ = importlib.machinery.ModuleSpec("rotary_embedding_torch", None)
+        m.RotaryEmbedding = type("RotaryEmbedding", (), {})
+        m.broadcat = None
+        sys.modules["rotary_embedding_torch"] = m
+    return importlib.import_module("tortoise_tts.models.clvp")
+
+
+def build_reference_clvp(sd, cfg):
+    """Reference CLVP at cfg's size with the synthetic weights loaded strictly, in eval mode."""
+    clvp = load_reference_clvp()
+    m = clvp.CLVP(dim_text=cfg.dim, dim_speech=cfg.dim, dim_latent=cfg.dim, num_text_tokens=cfg.num_text_tokens,
+                  text_enc_depth=cfg.depth, text_heads=cfg.heads, num_speech_tokens=cfg.num_speech_tokens,
+                  speech_enc_depth=cfg.depth, speech_heads=cfg.heads, use_xformers=True)
+    m.load_state_dict(sd, strict=True)
+    m.eval()
+    return m

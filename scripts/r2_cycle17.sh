@@ -1,0 +1,5 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_zz_no_alloc.py -m gpu -q -s > gpurun_out/pytest_noalloc_alone.log 2>&1; tail -6 gpurun_out/pytest_noalloc_alone.log
+timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; tail -4 gpurun_out/pytest_gpu.log
+bash scripts/r2_profile.sh

@@ -59,7 +59,23 @@ constexpr int kCtxOffsetFloats = 7168;
 // ---- hardware cluster barrier (all 256 threads of the 4 CTAs; ~0.2 us).  release/acquire at cluster scope: global
 // and distributed-shared writes made before it are visible to the cluster's threads after it. -----------------------
 __device__ __forceinline__ void cluster_barrier() {
+#ifdef TTS_CLUSTER_RELAXED_DIAG   // timing diagnostic only (results are NOT valid): what the release fence of the arrive costs
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;\n\tbarrier.cluster.wait.aligned;" ::: "memory");
+#else
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+#endif
+}
+
+// Timing diagnostic (TTS_CLUSTER_RELAXED_SITES = bit mask of call sites; results are NOT valid): which release fences cost what.
+template <int SITE>
+__device__ __forceinline__ void cluster_barrier_at() {
+#ifdef TTS_CLUSTER_RELAXED_SITES
+  if (TTS_CLUSTER_RELAXED_SITES & SITE) {
+    asm volatile("barrier.cluster.arrive.relaxed.aligned;\n\tbarrier.cluster.wait.aligned;" ::: "memory");
+    return;
+  }
+#endif
+  cluster_barrier();
 }
 
 // ---- weight feed: warp 0 of the CTA keeps the bulk-copy ring full --------------------------------------------------
@@ -916,7 +932,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
         ln_cluster(P, sm, layer == 0 ? LN_SRC_X : LN_SRC_XT, xtag, sm.red, is_head, rank, is_head ? 0 : tile_row0, ln_warps);
         if (!side && MODE != 4) prefetch_next(P, sm, head, pf_layer, C::kAttnRows, threadIdx.x, kDecThreads);
       }
-      cluster_barrier();
+      cluster_barrier_at<1>();
       prof_mark(P, c, 1);
       if (is_head) break;
       {
@@ -938,10 +954,10 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
                           }
                         });
       }
-      cluster_barrier();
+      cluster_barrier_at<2>();
       prof_mark(P, c, 200 + OP_ATTN);
       attn_local<MODE>(P, layer, head, attn_row0, ctx_row0, sm);
-      cluster_barrier();
+      cluster_barrier_at<4>();
       prof_mark(P, c, 200 + OP_PROJ);
       proj_splitk<MODE>(P, rank, row_lo, tile_row0, sm, pipe);
       // ---- phase B: ln_2 -> c_fc -> gelu_new ----
@@ -955,7 +971,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
         if (grp) cluster_barrier();       // every CTA of the cluster has multiplied the previous group's rows
         const int rbase = 16 * C::kMtB * grp;
         ln_cluster(P, sm, LN_SRC_Y, 1 + kH, sm.red + kStageOffLn2, false, rank, rbase, kNpcB);
-        cluster_barrier();
+        cluster_barrier_at<8>();
         prof_mark(P, c, 1);
         const float* bias = layer_f(P, layer) + kFOffBfc;
         const int t0 = blockIdx.x * 4;
