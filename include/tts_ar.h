@@ -228,6 +228,71 @@ int tts_ar_gemm_f32_noalloc(const float* a_f32, const void* wt_bf16, const float
  *   "prof_step"          decode step whose per-stage timestamps are recorded (scripts/stage_prof.py); -1 off */
 int tts_ar_set_option(TtsArHandle* h, const char* name, int32_t value);
 
+/* ---- CLVP candidate scoring -------------------------------------------------------------------------
+ * Replaces `clvp(text_tokens.repeat(n, 1), codes, return_loss=False)` of the reference (tortoise_tts/inference.py:392-396):
+ * CLVP.forward (tortoise_tts/models/clvp.py:100-133) in eval mode with use_xformers=True -- two pre-norm x-transformers
+ * encoders (RMSNorm, no-bias q/k/v, rotary embedding on the first 32 dims of q, k and v, full softmax attention, GLU
+ * feed-forward with exact GELU; xtransformers.py:337-346, 431-479, 583-731, 912-1016), final LayerNorm, mean over positions,
+ * to_*_latent, L2 normalisation, sim = <text, speech> * exp(temperature).  The caller keeps `torch.topk(scores, k)`.
+ * The GEMMs run on the tcgen05 kernel of the dense passes (csrc/tc_gemm.cuh) in bf16 with fp32 accumulation; the residual
+ * stream, norms, softmax and the latents are fp32.  Own handle: CLVP is a separate module with its own weights. */
+typedef struct TtsClvpHandle TtsClvpHandle;
+
+typedef struct {
+  int32_t struct_size;
+  int32_t device;
+  int32_t dim;                  /* 768: dim_text == dim_speech == dim_latent (clvp.py:31-33) */
+  int32_t heads;                /* 12 heads x 64 */
+  int32_t depth;                /* 20: text_enc_depth == speech_enc_depth */
+  int32_t n_text_tokens;        /* 256 */
+  int32_t n_speech_tokens;      /* 8192 */
+  int32_t max_seqs;             /* capacity: candidates per call */
+  int32_t max_text_len;         /* capacity: text tokens per row */
+  int32_t max_speech_len;       /* capacity: codes per candidate */
+} TtsClvpConfig;
+
+/* One (attention, feed-forward) pair of an encoder: reference keys
+ * {text,speech}_transformer.transformer.attn_layers.layers.{2i}.* and .{2i+1}.*; nn.Linear weights are [out, in]. */
+typedef struct {
+  const void* attn_norm_g;                   /* layers.{2i}.0.0.g          [768] */
+  const void *to_q_w, *to_k_w, *to_v_w;      /* layers.{2i}.1.wrap.to_*    [768,768], no bias */
+  const void *to_out_w, *to_out_b;           /* layers.{2i}.1.wrap.to_out  [768,768], [768] */
+  const void* ff_norm_g;                     /* layers.{2i+1}.0.0.g        [768] */
+  const void *ff_proj_w, *ff_proj_b;         /* layers.{2i+1}.1.wrap.net.0.proj  [3072,768], [3072] (value rows, then gate rows) */
+  const void *ff_out_w, *ff_out_b;           /* layers.{2i+1}.1.wrap.net.3       [768,1536], [768] */
+} TtsClvpLayerWeights;
+
+typedef struct {
+  const void* emb;                           /* {text,speech}_emb.weight [n_tokens, 768] */
+  const TtsClvpLayerWeights* layers;         /* host array of `depth` entries (dev pointers inside) */
+  const void *norm_w, *norm_b;               /* transformer.norm (final LayerNorm) */
+  const void* to_latent_w;                   /* to_{text,speech}_latent.weight [768,768], no bias */
+} TtsClvpEncoderWeights;
+
+typedef struct {
+  int32_t struct_size;
+  int32_t dtype;                             /* 0 = float32, 1 = bfloat16 (all tensors, dev pointers) */
+  int32_t depth;
+  TtsClvpEncoderWeights text, speech;
+  const void* temperature;                   /* scalar parameter (sim is multiplied by exp of it) */
+} TtsClvpWeights;
+
+int tts_ar_clvp_create(const TtsClvpConfig* cfg, TtsClvpHandle** out);     /* allocates; SYNC */
+void tts_ar_clvp_destroy(TtsClvpHandle* h);
+const char* tts_ar_clvp_last_error(TtsClvpHandle* h);                      /* h may be NULL: error of the last failed create */
+int tts_ar_clvp_load_weights(TtsClvpHandle* h, const TtsClvpWeights* w, void* stream);
+/* scores[i] = sim(text row (n_text == 1 ? 0 : i), codes row i), i < n.
+ *   text   dev int32 [n_text, text_stride], n_text == 1 (one text for every candidate) or n_text == n, text_len tokens each
+ *   codes  dev int64 [n, codes_stride] (the layout tts_ar_generate / tts_ar_fixup_codes leave), codes_len codes each
+ *   scores dev float32 [n];  speech_latents dev float32 [n, 768] or NULL: the L2-normalised speech latents (parity hook)
+ * ASYNC on `stream`; a token id outside its table is reported by tts_ar_clvp_sync (the reference's nn.Embedding raises). */
+int tts_ar_clvp_score(TtsClvpHandle* h, const int32_t* text, int32_t n_text, int32_t text_len, int32_t text_stride,
+                      const int64_t* codes, int32_t n, int32_t codes_len, int32_t codes_stride, float* scores,
+                      float* speech_latents, void* stream);
+/* Waits for `stream`; TTS_AR_ERR_BAD_ARG after an out-of-range token id, TTS_AR_ERR_WATCHDOG after a device-side time-out
+ * (each reported once and cleared).  *launches (nullable) = this library's kernel launches on the handle so far.  SYNC. */
+int tts_ar_clvp_sync(TtsClvpHandle* h, int64_t* launches, void* stream);
+
 /* Waits for `stream`, then reports the last call's outcome (TTS_AR_ERR_WATCHDOG after a device-side time-out,
  * TTS_AR_ERR_BAD_ARG when a token id was outside its embedding table -- the reference's nn.Embedding raises).
  * Either condition is reported once and cleared. SYNC. */

@@ -171,3 +171,29 @@ def test_typical_mass_rule_equals_reference_support(golden_dir):
                 thr = shifted[want[r]].max()
                 assert np.all(np.abs(shifted[diff] - thr) < 1e-6 * max(1.0, thr)), (mass, r, diff[:5])
                 assert diff.size <= 2
+
+
+# ---- CLVP candidate scoring: oracle/clvp_oracle.py vs the reference's CLVP class ----------------
+@pytest.mark.parametrize("case", ["d2", "d20"])
+def test_clvp_oracle_matches_the_reference_class(golden_dir, case):
+    """tests/golden/clvp.npz holds what the REFERENCE's CLVP.forward(text.repeat(n, 1), codes, return_loss=False)
+    (inference.py:392-396 call) returned on synthetic weights; the restatement must reproduce scores, top-k order and the
+    encoder outputs to fp32 round-off."""
+    import ast
+    from oracle.clvp_oracle import ClvpConfig, OracleCLVP, make_clvp_inputs, make_clvp_state_dict
+    g = np.load(os.path.join(golden_dir, "clvp.npz"))
+    spec = ast.literal_eval(str(g[f"{case}_spec"]))
+    cfg = ClvpConfig(depth=spec["depth"])
+    sd = make_clvp_state_dict(cfg, seed=spec["w_seed"])
+    text, codes = make_clvp_inputs(cfg, spec["n"], spec["text_len"], spec["speech_len"], seed=spec["in_seed"])
+    o = OracleCLVP(sd, cfg)
+    scores = o.score(text, codes)
+    want = torch.from_numpy(g[f"{case}_scores"])
+    assert (scores - want).abs().max() < 2e-5, (scores - want).abs().max()
+    assert torch.topk(scores, k=min(spec["n"], 4)).indices.tolist() == g[f"{case}_topk"].tolist()
+    with torch.inference_mode():
+        enc = o.encode("speech", codes[:1])[0]
+        enc_t = o.encode("text", text)[0]
+    ws, wt = torch.from_numpy(g[f"{case}_enc_speech_row0"]), torch.from_numpy(g[f"{case}_enc_text"])
+    assert (enc[: ws.shape[0]] - ws).abs().max() < 2e-4
+    assert (enc_t[: wt.shape[0]] - wt).abs().max() < 2e-4

@@ -15,6 +15,8 @@ SYMBOLS = [
     "tts_ar_inference_speech_host", "tts_ar_sync_result", "tts_ar_debug_copy", "tts_ar_fixup_codes",
     "tts_ar_debug_gemm", "tts_ar_set_option", "tts_ar_stream_begin", "tts_ar_stream_poll", "tts_ar_stream_end",
     "tts_ar_gemm_f32_noalloc",
+    "tts_ar_clvp_create", "tts_ar_clvp_destroy", "tts_ar_clvp_last_error", "tts_ar_clvp_load_weights", "tts_ar_clvp_score",
+    "tts_ar_clvp_sync",
 ]
 
 ABI_VERSION = 2
@@ -55,6 +57,28 @@ class TtsArStats(C.Structure):
                 ("kv_pages", C.c_int32), ("ctas", C.c_int32)]
 
 
+class TtsClvpConfig(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in (
+        "struct_size", "device", "dim", "heads", "depth", "n_text_tokens", "n_speech_tokens", "max_seqs", "max_text_len",
+        "max_speech_len")]
+
+
+class TtsClvpLayerWeights(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in (
+        "attn_norm_g", "to_q_w", "to_k_w", "to_v_w", "to_out_w", "to_out_b", "ff_norm_g", "ff_proj_w", "ff_proj_b",
+        "ff_out_w", "ff_out_b")]
+
+
+class TtsClvpEncoderWeights(C.Structure):
+    _fields_ = [("emb", C.c_void_p), ("layers", C.POINTER(TtsClvpLayerWeights)), ("norm_w", C.c_void_p),
+                ("norm_b", C.c_void_p), ("to_latent_w", C.c_void_p)]
+
+
+class TtsClvpWeights(C.Structure):
+    _fields_ = [("struct_size", C.c_int32), ("dtype", C.c_int32), ("depth", C.c_int32),
+                ("text", TtsClvpEncoderWeights), ("speech", TtsClvpEncoderWeights), ("temperature", C.c_void_p)]
+
+
 _lib = None
 
 
@@ -85,6 +109,14 @@ def load():
                                                  C.POINTER(TtsArSampling), i32, i64p, C.POINTER(C.c_int32), vp]
     lib.tts_ar_debug_gemm.argtypes = [vp, vp, vp, f32p, f32p, i32, i32, i32, i32, vp]
     lib.tts_ar_gemm_f32_noalloc.argtypes = [f32p, vp, f32p, f32p, i32, i32, i32, i32, i32p, vp]
+    lib.tts_ar_clvp_create.argtypes = [C.POINTER(TtsClvpConfig), C.POINTER(vp)]
+    lib.tts_ar_clvp_destroy.argtypes = [vp]
+    lib.tts_ar_clvp_destroy.restype = None
+    lib.tts_ar_clvp_last_error.argtypes = [vp]
+    lib.tts_ar_clvp_last_error.restype = C.c_char_p
+    lib.tts_ar_clvp_load_weights.argtypes = [vp, C.POINTER(TtsClvpWeights), vp]
+    lib.tts_ar_clvp_score.argtypes = [vp, i32p, i32, i32, i32, i64p, i32, i32, i32, f32p, f32p, vp]
+    lib.tts_ar_clvp_sync.argtypes = [vp, C.POINTER(C.c_int64), vp]
     lib.tts_ar_set_option.argtypes = [vp, C.c_char_p, i32]
     lib.tts_ar_stream_begin.argtypes = [vp, C.POINTER(TtsArSampling), i32, i64p, f32p, vp]
     lib.tts_ar_stream_poll.argtypes = [vp, i32, i32]
@@ -94,7 +126,7 @@ def load():
     lib.tts_ar_fixup_codes.argtypes = [vp, i64p, i32, i32, i32, i32, i32p, i32p, vp]
     for s in SYMBOLS:
         getattr(lib, s)
-        if s not in ("tts_ar_destroy", "tts_ar_last_error"):
+        if s not in ("tts_ar_destroy", "tts_ar_last_error", "tts_ar_clvp_destroy", "tts_ar_clvp_last_error"):
             getattr(lib, s).restype = C.c_int
     assert lib.tts_ar_abi_version() == ABI_VERSION
     _lib = lib

@@ -22,7 +22,10 @@ enum TcEpi : int {
   TC_EPI_STORE = 0,   // out_f32[row][col] = acc + bias          (mel head logits; bring-up test)
   TC_EPI_RESID = 1,   // x[row][col] += acc + bias                (attn.c_proj, mlp.c_proj)
   TC_EPI_GELU = 2,    // out_bf16[row][col] = gelu_new(acc + bias) (c_fc)
-  TC_EPI_QKV = 3      // q (fp32, pre-scaled 1/8) and the K/V page slots of the row's position (c_attn)
+  TC_EPI_QKV = 3,     // q (fp32, pre-scaled 1/8) and the K/V page slots of the row's position (c_attn)
+  TC_EPI_ROT = 4,     // CLVP q|k|v: out_bf16[row][col] = acc, rotary embedding on the first 32 dims of every 64-dim head
+  TC_EPI_GLU = 5      // CLVP feed-forward: out_bf16[row][u] = (acc_x + b) * gelu_erf(acc_gate + b); weight rows interleaved
+                      // per 32 hidden units (x block, gate block) so both halves of a unit sit in one tile (clvp.cu)
 };
 
 struct TcGemmArgs {
@@ -39,6 +42,9 @@ struct TcGemmArgs {
   const int* prefix_pt;        // [utts][kMaxPagesPerSeg]
   int n_pages, layer;
   int* watchdog;               // device flag: a wait timed out
+  // ROT
+  const float* rot_tab;        // [seq_len][32]: cos(pos * inv_freq[i]) for i < 16, then sin
+  int seq_len;                 // rows per sequence (position of a row = row % seq_len)
 };
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------------------
@@ -173,6 +179,31 @@ __device__ __forceinline__ void tc_epilogue(const TcGemmArgs& g, int row, int co
       pk.w = pack_bf16x2(gelu_new(v[i + 6]), gelu_new(v[i + 7]));
       *reinterpret_cast<uint4*>(o + i) = pk;
     }
+  } else if (EPI == TC_EPI_ROT) {
+    // reference xtransformers.py:279-290, 660-664: rotary dims = the first 32 of each head, dim i pairs with dim i + 16,
+    // applied to q, k AND v; a 32-column chunk starting at a multiple of 64 is exactly the rotary part of one head
+    if ((col & 63) == 0) {
+      const float* rt = g.rot_tab + (size_t)(row % g.seq_len) * 32;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const float c = rt[i], sn = rt[16 + i];
+        const float a = v[i], b = v[i + 16];
+        v[i] = a * c - b * sn;
+        v[i + 16] = b * c + a * sn;
+      }
+    }
+    __nv_bfloat16* o = g.out_bf16 + (size_t)row * g.N + col;
+#pragma unroll
+    for (int i = 0; i < 32; i += 8) {
+      uint4 pk;
+      pk.x = pack_bf16x2(v[i], v[i + 1]);
+      pk.y = pack_bf16x2(v[i + 2], v[i + 3]);
+      pk.z = pack_bf16x2(v[i + 4], v[i + 5]);
+      pk.w = pack_bf16x2(v[i + 6], v[i + 7]);
+      *reinterpret_cast<uint4*>(o + i) = pk;
+    }
+  } else if (EPI == TC_EPI_GLU) {
+    // handled by tc_epilogue_glu (two chunks at a time)
   } else {   // TC_EPI_QKV: columns [0,1024) query, [1024,2048) key, [2048,3072) value; 32 columns never straddle a head
     const int part = col >> 10, cc = col & (kD - 1);
     if (part == 0) {
@@ -195,6 +226,26 @@ __device__ __forceinline__ void tc_epilogue(const TcGemmArgs& g, int row, int co
         *reinterpret_cast<uint4*>(o + i) = pk;
       }
     }
+  }
+}
+
+// GLU epilogue of one thread: x chunk r0 (columns col .. col + 31 of the interleaved image) and its gate chunk r1 (col + 32 ..):
+// hidden units (col >> 1) .. + 31.  exact (erf) GELU as nn.GELU() (reference xtransformers.py:431-440, 455).
+__device__ __forceinline__ void tc_epilogue_glu(const TcGemmArgs& g, int row, int col, const uint32_t (&r0)[32], const uint32_t (&r1)[32]) {
+  if (row >= g.M || col >= g.N) return;
+  __nv_bfloat16* o = g.out_bf16 + (size_t)row * (g.N >> 1) + (col >> 1);
+#pragma unroll
+  for (int i = 0; i < 32; i += 8) {
+    float h[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float x = __uint_as_float(r0[i + k]) + g.bias[col + i + k];
+      const float t = __uint_as_float(r1[i + k]) + g.bias[col + 32 + i + k];
+      h[k] = x * (0.5f * t * (1.0f + erff(t * 0.70710678118654752f)));
+    }
+    uint4 pk;
+    pk.x = pack_bf16x2(h[0], h[1]); pk.y = pack_bf16x2(h[2], h[3]); pk.z = pack_bf16x2(h[4], h[5]); pk.w = pack_bf16x2(h[6], h[7]);
+    *reinterpret_cast<uint4*>(o + i) = pk;
   }
 }
 
@@ -277,11 +328,21 @@ __global__ void __launch_bounds__(192, 1) tc_gemm_kernel(const __grid_constant__
       tc_fence_after();
       const int row = m_idx + ew * 32 + lane;
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(ew * 32) << 16);
+      if (EPI == TC_EPI_GLU) {
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32(taddr + c0, r);
-        tc_epilogue<EPI>(g, row, n_idx + c0, r);
+        for (int c0 = 0; c0 < BN; c0 += 64) {
+          uint32_t r0[32], r1[32];
+          tmem_ld_32x32(taddr + c0, r0);
+          tmem_ld_32x32(taddr + c0 + 32, r1);
+          tc_epilogue_glu(g, row, n_idx + c0, r0, r1);
+        }
+      } else {
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+          uint32_t r[32];
+          tmem_ld_32x32(taddr + c0, r);
+          tc_epilogue<EPI>(g, row, n_idx + c0, r);
+        }
       }
       tc_fence_before();
       __syncwarp();

@@ -90,3 +90,62 @@ def make_inputs(cfg: ARConfig, n_utt: int, text_lens, seed: int = 1):
     texts = [torch.randint(1, cfg.number_text_tokens, (int(t),), generator=g, dtype=torch.long)
              for t in text_lens]
     return latent, texts
+
+
+# ---- CLVP (candidate scoring): reference tortoise_tts/models/clvp.py state_dict keys ----------------
+@dataclass
+class ClvpConfig:
+    dim: int = 768
+    heads: int = 12
+    depth: int = 20                     # both encoders (clvp.py:33,38)
+    num_text_tokens: int = 256
+    num_speech_tokens: int = 8192
+    dim_head: int = 64
+    rotary_dim: int = 32
+    ff_inner: int = 1536                # dim * ff_mult (2)
+
+
+def make_clvp_state_dict(cfg: ClvpConfig, seed=0, bf16=True):
+    """Synthetic weights under the reference's state_dict keys, drawn like the reference's default initialisers
+    (N(0,1) embeddings, U(+-1/sqrt(fan_in)) linears) so that activations have realistic scales; `bf16` rounds every
+    tensor to a bf16-representable value (the fp32 reference and the bf16 CUDA path then hold identical weights)."""
+    g = torch.Generator().manual_seed(seed)
+    sd = {}
+
+    def lin(out_f, in_f):
+        b = in_f ** -0.5
+        return (torch.rand(out_f, in_f, generator=g) * 2 - 1) * b
+
+    def vec(n, scale):
+        return torch.randn(n, generator=g) * scale
+
+    sd["temperature"] = torch.tensor(1.0)
+    for side, n_tok in (("text", cfg.num_text_tokens), ("speech", cfg.num_speech_tokens)):
+        sd[f"{side}_emb.weight"] = torch.randn(n_tok, cfg.dim, generator=g)
+        sd[f"to_{side}_latent.weight"] = lin(cfg.dim, cfg.dim)
+        p = f"{side}_transformer.transformer."
+        for i in range(cfg.depth):
+            a, f = f"{p}attn_layers.layers.{2 * i}.", f"{p}attn_layers.layers.{2 * i + 1}."
+            sd[a + "0.0.g"] = 1 + vec(cfg.dim, 0.1)
+            for n in ("to_q", "to_k", "to_v"):
+                sd[a + f"1.wrap.{n}.weight"] = lin(cfg.heads * cfg.dim_head, cfg.dim)
+            sd[a + "1.wrap.to_out.weight"] = lin(cfg.dim, cfg.heads * cfg.dim_head)
+            sd[a + "1.wrap.to_out.bias"] = vec(cfg.dim, 0.02)
+            sd[f + "0.0.g"] = 1 + vec(cfg.dim, 0.1)
+            sd[f + "1.wrap.net.0.proj.weight"] = lin(2 * cfg.ff_inner, cfg.dim)
+            sd[f + "1.wrap.net.0.proj.bias"] = vec(2 * cfg.ff_inner, 0.02)
+            sd[f + "1.wrap.net.3.weight"] = lin(cfg.dim, cfg.ff_inner)
+            sd[f + "1.wrap.net.3.bias"] = vec(cfg.dim, 0.02)
+        sd[p + "attn_layers.rotary_pos_emb.inv_freq"] = 1.0 / (10000 ** (torch.arange(0, cfg.rotary_dim, 2).float() / cfg.rotary_dim))
+        sd[p + "norm.weight"] = 1 + vec(cfg.dim, 0.1)
+        sd[p + "norm.bias"] = vec(cfg.dim, 0.02)
+    if bf16:
+        sd = {k: (v if k.endswith("inv_freq") else v.bfloat16().float()) for k, v in sd.items()}
+    return sd
+
+
+def make_clvp_inputs(cfg: ClvpConfig, n, text_len, speech_len, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    text = torch.randint(1, cfg.num_text_tokens, (1, text_len), generator=g)
+    codes = torch.randint(0, cfg.num_speech_tokens, (n, speech_len), generator=g)
+    return text, codes
