@@ -388,6 +388,51 @@ def streaming_latency(cfg, sd, dev):
     return res
 
 
+def clvp_scoring(dev, peaks, with_reference):
+    """the CLVP scoring call that follows the C2 job (reference inference.py:392-396): 16 candidates x 500
+    codes against one 64-token text, 20-layer encoders, random-init weights.  Device-timed (CUDA events), plus -- when the
+    baseline legs are on -- the reference math (oracle, torch eager fp32) on the same GPU."""
+    import torch
+    from tortoise_tts_b200.clvp import CLVPB200
+    from tortoise_tts_b200.synthetic import ClvpConfig, make_clvp_inputs, make_clvp_state_dict
+    ccfg = ClvpConfig()
+    csd = make_clvp_state_dict(ccfg, seed=5)
+    text, codes = make_clvp_inputs(ccfg, N_CAND, TEXT_LEN, MAX_NEW, seed=6)
+    text, codes = text.to(dev), codes.to(dev)
+    m = CLVPB200(csd, depth=ccfg.depth, device=dev, max_seqs=N_CAND, max_text_len=TEXT_LEN, max_speech_len=MAX_NEW)
+    m(text, codes)                                            # warm-up
+    l0 = m.kernel_launches
+    reps = 5
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    e0.record()
+    for _ in range(reps):
+        scores = m(text, codes)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / reps
+    rows = N_CAND * MAX_NEW + TEXT_LEN
+    flops = ccfg.depth * (rows * 2.0 * (768 * 6144 + 1536 * 768) + 4.0 * 64 * 12 * (N_CAND * MAX_NEW ** 2 + TEXT_LEN ** 2))
+    tens = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1400.0)))
+    rec = {"workload": f"{N_CAND} candidates x {MAX_NEW} codes, {TEXT_LEN} text tokens, 2 x {ccfg.depth} layers, d=768",
+           "ms": round(ms, 3), "rows": rows, "tflops": round(flops / (ms * 1e-3) / 1e12, 1),
+           "frac_of_bf16_sustained_peak": round(flops / (ms * 1e-3) / 1e12 / tens, 4),
+           "kernel_launches_per_call": int((m.kernel_launches - l0) / reps), "top4": torch.topk(scores, 4).indices.tolist(),
+           "how": "CUDA events around 5 calls of CLVPB200.forward (each ends with a stream sync), device-resident inputs"}
+    m.close()
+    if with_reference:
+        from oracle.clvp_oracle import OracleCLVP
+        o = OracleCLVP({k: v.to(dev) for k, v in csd.items()}, ccfg)
+        o.score(text, codes)
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        want = o.score(text, codes)
+        torch.cuda.synchronize(dev)
+        rec["reference_same_gpu_fp32_ms"] = round((time.perf_counter() - t0) * 1e3, 2)
+        rec["score_abs_err_vs_reference_math"] = round(float((scores - want).abs().max()), 6)
+    return rec
+
+
 def reference_same_gpu(cfg, sd, dev):
     """The oracle (reference math in torch eager; HF-style torch.cat KV cache, one host sync per step for the sampler, like the
     reference's sample_stream) on this GPU, fp32 and bf16: prompt pass + REF_SAMPLE_TOKENS sampled tokens x 16 candidates."""
@@ -566,6 +611,11 @@ def run_ours(args):
                 line["streaming"] = streaming_latency(cfg, sd, dev)
             except Exception as e:
                 line["streaming"] = {"unavailable": repr(e)[:200]}
+        if not args.no_sub_configs:
+            try:
+                line["clvp_scoring"] = clvp_scoring(dev, peaks_all, not args.no_cpu_baseline)
+            except Exception as e:
+                line["clvp_scoring"] = {"unavailable": repr(e)[:200]}
         if not args.no_cpu_baseline:
             try:
                 line["reference_same_gpu"] = reference_same_gpu(cfg, sd, dev)
