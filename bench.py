@@ -421,15 +421,19 @@ def clvp_scoring(dev, peaks, with_reference):
            "how": "CUDA events around 5 calls of CLVPB200.forward (each ends with a stream sync), device-resident inputs"}
     m.close()
     if with_reference:
-        from oracle.clvp_oracle import OracleCLVP
-        o = OracleCLVP({k: v.to(dev) for k, v in csd.items()}, ccfg)
-        o.score(text, codes)
-        torch.cuda.synchronize(dev)
-        t0 = time.perf_counter()
-        want = o.score(text, codes)
-        torch.cuda.synchronize(dev)
-        rec["reference_same_gpu_fp32_ms"] = round((time.perf_counter() - t0) * 1e3, 2)
-        rec["score_abs_err_vs_reference_math"] = round(float((scores - want).abs().max()), 6)
+        try:
+            from oracle.clvp_oracle import OracleCLVP
+            o = OracleCLVP({k: v.to(dev) for k, v in csd.items()}, ccfg)
+            o.score(text, codes)
+            torch.cuda.synchronize(dev)
+            t0 = time.perf_counter()
+            want = o.score(text, codes)
+            torch.cuda.synchronize(dev)
+            rec["reference_same_gpu_fp32_ms"] = round((time.perf_counter() - t0) * 1e3, 2)
+            rec["score_abs_err_vs_reference_math"] = round(float((scores - want).abs().max()), 6)
+        except Exception as e:
+            rec["reference_same_gpu_fp32_ms"] = None
+            rec["reference_unavailable"] = repr(e)[:160]
     return rec
 
 

@@ -228,6 +228,35 @@ int tts_ar_gemm_f32_noalloc(const float* a_f32, const void* wt_bf16, const float
  *   "prof_step"          decode step whose per-stage timestamps are recorded (scripts/stage_prof.py); -1 off */
 int tts_ar_set_option(TtsArHandle* h, const char* name, int32_t value);
 
+/* ---- conditioning-latent encoder ---------------------------------------------------------------------
+ * Replaces UnifiedVoice.get_conditioning (reference tortoise_tts/models/unified_voice.py:535-542, called once per voice by
+ * tortoise_tts/emb/mel.py:97): ConditioningEncoder (:269-293) = 1x1 conv 80 -> 1024, then 6 AttentionBlocks
+ * (tortoise_tts/models/arch_utils.py:136-190: GroupNorm32(32 groups), qkv 1x1 conv, QKVAttentionLegacy :59-95 with 16 heads,
+ * proj_out 1x1 conv, residual), column 0 of the result, mean over the clips.  The 1x1 convolutions of the blocks run on the
+ * tcgen05 GEMM (bf16 operands, fp32 accumulation); the init conv, GroupNorm statistics, softmax and the residual are fp32.
+ * Weights are `conditioning_encoder.*` of the same state_dict, so the entry points live on the AR handle and use its
+ * activation buffers: frames <= the handle's row capacity (>= max_text_len + max_new_tokens + 5), and a call invalidates a
+ * pending tts_ar_prefill (prefill again before generating -- the reference computes the latent before the AR call too). */
+typedef struct {
+  const void *norm_w, *norm_b;          /* attn.{i}.norm      [1024] */
+  const void *qkv_w, *qkv_b;            /* attn.{i}.qkv       [3072,1024,1], [3072]; channel = head * 192 + {q,k,v} * 64 + c */
+  const void *proj_w, *proj_b;          /* attn.{i}.proj_out  [1024,1024,1], [1024] */
+} TtsArCondBlockWeights;
+
+typedef struct {
+  int32_t struct_size;
+  int32_t dtype;                        /* 0 = float32, 1 = bfloat16 (all tensors, dev pointers) */
+  int32_t n_blocks;                     /* 6 */
+  int32_t spec_dim;                     /* 80 mel bins */
+  const void *init_w, *init_b;          /* init [1024,spec_dim,1], [1024] */
+  const TtsArCondBlockWeights* blocks;  /* host array of n_blocks entries */
+} TtsArCondWeights;
+
+int tts_ar_load_conditioning_weights(TtsArHandle* h, const TtsArCondWeights* w, void* stream);
+/*   mel     dev float32 [n_clips, spec_dim, frames]  (speech_conditioning_input[b] of the reference)
+ *   latent  dev float32 [1024]: mean over the clips of column 0 of the encoder output.  ASYNC on `stream`. */
+int tts_ar_get_conditioning(TtsArHandle* h, const float* mel, int32_t n_clips, int32_t frames, float* latent, void* stream);
+
 /* ---- CLVP candidate scoring -------------------------------------------------------------------------
  * Replaces `clvp(text_tokens.repeat(n, 1), codes, return_loss=False)` of the reference (tortoise_tts/inference.py:392-396):
  * CLVP.forward (tortoise_tts/models/clvp.py:100-133) in eval mode with use_xformers=True -- two pre-norm x-transformers

@@ -47,7 +47,7 @@ class OracleCLVP:
         x = sd[f"{side}_emb.weight"][tokens]
         b, n, _ = x.shape
         inv = sd[p + "attn_layers.rotary_pos_emb.inv_freq"]
-        fr = torch.arange(n).float()[:, None] * inv[None, :]
+        fr = torch.arange(n, device=inv.device).float()[:, None] * inv[None, :]
         freqs = torch.cat((fr, fr), dim=-1)[None, None]                    # [1, 1, n, 32]
 
         def rms(v, g):

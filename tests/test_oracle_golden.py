@@ -197,3 +197,17 @@ def test_clvp_oracle_matches_the_reference_class(golden_dir, case):
     ws, wt = torch.from_numpy(g[f"{case}_enc_speech_row0"]), torch.from_numpy(g[f"{case}_enc_text"])
     assert (enc[: ws.shape[0]] - ws).abs().max() < 2e-4
     assert (enc_t[: wt.shape[0]] - wt).abs().max() < 2e-4
+
+
+# ---- conditioning-latent encoder: oracle/cond_oracle.py vs the reference's get_conditioning --------
+@pytest.mark.parametrize("case", ["one_clip", "two_clips"])
+def test_conditioning_oracle_matches_the_reference_class(golden_dir, case):
+    import ast
+    from oracle.cond_oracle import OracleConditioning, make_cond_mel, make_cond_state_dict
+    g = np.load(os.path.join(golden_dir, "cond.npz"))
+    spec = ast.literal_eval(str(g[f"{case}_spec"]))
+    o = OracleConditioning(make_cond_state_dict(seed=spec["w_seed"]))
+    lat = o.get_conditioning(make_cond_mel(spec["batch"], spec["clips"], spec["frames"], seed=spec["in_seed"]))
+    want = torch.from_numpy(g[f"{case}_latent"])
+    assert lat.shape == want.shape == (spec["batch"], 1024)
+    assert rel(lat.numpy(), want.numpy()) < FP32_REL

@@ -16,7 +16,7 @@ SYMBOLS = [
     "tts_ar_debug_gemm", "tts_ar_set_option", "tts_ar_stream_begin", "tts_ar_stream_poll", "tts_ar_stream_end",
     "tts_ar_gemm_f32_noalloc",
     "tts_ar_clvp_create", "tts_ar_clvp_destroy", "tts_ar_clvp_last_error", "tts_ar_clvp_load_weights", "tts_ar_clvp_score",
-    "tts_ar_clvp_sync",
+    "tts_ar_clvp_sync", "tts_ar_load_conditioning_weights", "tts_ar_get_conditioning",
 ]
 
 ABI_VERSION = 2
@@ -55,6 +55,15 @@ class TtsArStats(C.Structure):
                 ("watchdog", C.c_int32), ("kernel_launches", C.c_int64), ("last_algorithmic_bytes", C.c_double),
                 ("last_device_ms", C.c_float), ("last_prefill_ms", C.c_float),
                 ("kv_pages", C.c_int32), ("ctas", C.c_int32)]
+
+
+class TtsArCondBlockWeights(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("norm_w", "norm_b", "qkv_w", "qkv_b", "proj_w", "proj_b")]
+
+
+class TtsArCondWeights(C.Structure):
+    _fields_ = [("struct_size", C.c_int32), ("dtype", C.c_int32), ("n_blocks", C.c_int32), ("spec_dim", C.c_int32),
+                ("init_w", C.c_void_p), ("init_b", C.c_void_p), ("blocks", C.POINTER(TtsArCondBlockWeights))]
 
 
 class TtsClvpConfig(C.Structure):
@@ -109,6 +118,8 @@ def load():
                                                  C.POINTER(TtsArSampling), i32, i64p, C.POINTER(C.c_int32), vp]
     lib.tts_ar_debug_gemm.argtypes = [vp, vp, vp, f32p, f32p, i32, i32, i32, i32, vp]
     lib.tts_ar_gemm_f32_noalloc.argtypes = [f32p, vp, f32p, f32p, i32, i32, i32, i32, i32p, vp]
+    lib.tts_ar_load_conditioning_weights.argtypes = [vp, C.POINTER(TtsArCondWeights), vp]
+    lib.tts_ar_get_conditioning.argtypes = [vp, f32p, i32, i32, f32p, vp]
     lib.tts_ar_clvp_create.argtypes = [C.POINTER(TtsClvpConfig), C.POINTER(vp)]
     lib.tts_ar_clvp_destroy.argtypes = [vp]
     lib.tts_ar_clvp_destroy.restype = None

@@ -182,7 +182,7 @@ __device__ __forceinline__ void tc_epilogue(const TcGemmArgs& g, int row, int co
   } else if (EPI == TC_EPI_ROT) {
     // reference xtransformers.py:279-290, 660-664: rotary dims = the first 32 of each head, dim i pairs with dim i + 16,
     // applied to q, k AND v; a 32-column chunk starting at a multiple of 64 is exactly the rotary part of one head
-    if ((col & 63) == 0) {
+    if (g.rot_tab && (col & 63) == 0) {   // rot_tab == nullptr: plain bf16 store (conditioning encoder q|k|v)
       const float* rt = g.rot_tab + (size_t)(row % g.seq_len) * 32;
 #pragma unroll
       for (int i = 0; i < 16; ++i) {

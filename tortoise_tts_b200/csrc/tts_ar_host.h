@@ -23,6 +23,20 @@ struct DenseW {
   CUtensorMap a_xn, a_ctx, a_h;       // activation buffers as A operands (row-major bf16 in this path)
 };
 
+// conditioning-latent encoder (cond_enc.cu): fp32 vectors + K-major bf16 images of the 1x1 convolutions of the attention blocks
+struct CondW {
+  bool loaded = false;
+  int n_blocks = 0, spec_dim = 0;
+  float *init_wt = nullptr, *init_b = nullptr;      // init conv, transposed [spec_dim][1024]; bias
+  float* stats = nullptr;                           // GroupNorm (mean, rstd) per group [32][2]
+  struct Block {
+    float *gn_w, *gn_b, *b_qkv, *b_proj;
+    __nv_bfloat16 *qkv, *proj;                      // [3072][1024] rows reordered to q | k | v, [1024][1024]
+    CUtensorMap m_qkv[2], m_proj[2];
+  };
+  std::vector<Block> blocks;
+};
+
 constexpr int kMaxGroups = 16;   // a batch runs as at most this many consecutive head-cluster launches of <= 64 sequences
 
 struct TtsArHandle {
@@ -56,6 +70,7 @@ struct TtsArHandle {
   float *d_mel_emb = nullptr, *d_mel_pos = nullptr, *d_text_emb = nullptr, *d_text_pos = nullptr;
 
   DenseW dense;
+  CondW cond;
 
   // activations / cache (device)
   long long* d_y = nullptr;            // cluster decode kernels: attention-block counting accumulator [64][1024]

@@ -149,3 +149,32 @@ def make_clvp_inputs(cfg: ClvpConfig, n, text_len, speech_len, seed=0):
     text = torch.randint(1, cfg.num_text_tokens, (1, text_len), generator=g)
     codes = torch.randint(0, cfg.num_speech_tokens, (n, speech_len), generator=g)
     return text, codes
+
+
+# ---- conditioning-latent encoder: reference unified_voice.py:269-293 state_dict keys ------------------
+def make_cond_state_dict(seed: int = 0, dim: int = 1024, spec_dim: int = 80, blocks: int = 6, bf16: bool = True):
+    """`conditioning_encoder.*` entries of UnifiedVoice.state_dict(): init 1x1 conv, then per AttentionBlock GroupNorm
+    gain/bias, qkv 1x1 conv, proj_out 1x1 conv.  proj_out is zero-initialised in the reference (zero_module, arch_utils.py:171):
+    with that default every block is the identity, so the synthetic values are drawn non-zero.  `bf16` rounds the GEMM weights
+    (qkv, proj_out) to bf16-representable values so that the fp32 reference and the CUDA path hold identical weights."""
+    g = torch.Generator().manual_seed(seed)
+    p = "conditioning_encoder."
+    sd = {p + "init.weight": (torch.rand(dim, spec_dim, 1, generator=g) * 2 - 1) * spec_dim ** -0.5,
+          p + "init.bias": torch.randn(dim, generator=g) * 0.05}
+    for i in range(blocks):
+        a = f"{p}attn.{i}."
+        sd[a + "norm.weight"] = 1 + torch.randn(dim, generator=g) * 0.1
+        sd[a + "norm.bias"] = torch.randn(dim, generator=g) * 0.05
+        sd[a + "qkv.weight"] = torch.randn(3 * dim, dim, 1, generator=g) * 0.06
+        sd[a + "qkv.bias"] = torch.randn(3 * dim, generator=g) * 0.02
+        sd[a + "proj_out.weight"] = torch.randn(dim, dim, 1, generator=g) * 0.03
+        sd[a + "proj_out.bias"] = torch.randn(dim, generator=g) * 0.02
+    if bf16:
+        sd = {k: (v.bfloat16().float() if k.endswith(("qkv.weight", "proj_out.weight")) else v) for k, v in sd.items()}
+    return sd
+
+
+def make_cond_mel(n_batch: int, n_clips: int, frames: int, seed: int = 0, spec_dim: int = 80):
+    """A mel-spectrogram-shaped input [n_batch, n_clips, 80, frames]: log-mel values are roughly in [-11.5, 2]."""
+    g = torch.Generator().manual_seed(seed)
+    return torch.randn(n_batch, n_clips, spec_dim, frames, generator=g) * 2.0 - 5.0

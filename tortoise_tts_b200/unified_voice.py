@@ -169,7 +169,45 @@ class UnifiedVoiceB200:
         w.text_pos_embedding = dev("text_pos_embedding.emb.weight")
         torch.cuda.synchronize(self.device)
         self._check(self.lib.tts_ar_load_weights(self.handle, C.byref(w), self._stream()), "tts_ar_load_weights")
+        # the conditioning-latent encoder, when the state_dict carries it (the AR path itself does not need it)
+        self.has_conditioning_encoder = "conditioning_encoder.init.weight" in sd
+        if self.has_conditioning_encoder:
+            n_blocks = 1 + max(int(k.split(".")[2]) for k in sd if k.startswith("conditioning_encoder.attn."))
+            blocks = (_lib.TtsArCondBlockWeights * n_blocks)()
+            for i in range(n_blocks):
+                a = f"conditioning_encoder.attn.{i}."
+                b = blocks[i]
+                b.norm_w, b.norm_b = dev(a + "norm.weight"), dev(a + "norm.bias")
+                b.qkv_w, b.qkv_b = dev(a + "qkv.weight"), dev(a + "qkv.bias")
+                b.proj_w, b.proj_b = dev(a + "proj_out.weight"), dev(a + "proj_out.bias")
+            cw = _lib.TtsArCondWeights()
+            cw.struct_size, cw.dtype, cw.n_blocks = C.sizeof(cw), w.dtype, n_blocks
+            cw.spec_dim = sd["conditioning_encoder.init.weight"].shape[1]
+            cw.init_w, cw.init_b = dev("conditioning_encoder.init.weight"), dev("conditioning_encoder.init.bias")
+            cw.blocks = blocks
+            torch.cuda.synchronize(self.device)
+            self._check(self.lib.tts_ar_load_conditioning_weights(self.handle, C.byref(cw), self._stream()),
+                        "tts_ar_load_conditioning_weights")
+        torch.cuda.synchronize(self.device)
         del keep
+
+    def get_conditioning(self, speech_conditioning_input):
+        """UnifiedVoice.get_conditioning (unified_voice.py:535-542): [b, n_clips, 80, frames] (or [b, 80, frames]) mel
+        spectrograms -> [b, 1024] conditioning latents (mean over the clips of column 0 of the conditioning encoder)."""
+        if not getattr(self, "has_conditioning_encoder", False):
+            raise RuntimeError("the state_dict this model was built from has no conditioning_encoder.* entries")
+        x = speech_conditioning_input
+        x = x.unsqueeze(1) if x.dim() == 3 else x
+        if x.dim() != 4:
+            raise ValueError("speech_conditioning_input must be [b, n_clips, spec, frames] or [b, spec, frames]")
+        x = x.to(device=self.device, dtype=torch.float32).contiguous()
+        out = torch.empty(x.shape[0], self.geometry.model_dim, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            for b in range(x.shape[0]):
+                self._check(self.lib.tts_ar_get_conditioning(self.handle, _ptr(x[b]), x.shape[1], x.shape[3], _ptr(out[b]), self._stream()),
+                            "tts_ar_get_conditioning")
+            self.sync_stats()
+        return out
 
     # ---- helpers ----------------------------------------------------------------------------------------
     def _sampling(self, kw):
