@@ -458,6 +458,8 @@ def patch_reference_module(module, **kw):
     module.inference_speech = impl.inference_speech
     module.compute_embeddings = impl.compute_embeddings
     module.get_generator = impl.get_generator
+    if impl.has_conditioning_encoder:
+        module.get_conditioning = impl.get_conditioning
     orig_forward = module.forward
 
     def forward(*a, **k):
