@@ -12,7 +12,8 @@ constexpr int kLnSplitMinRows = 16;   // interpreter: LayerNorm as its own grid-
 struct Ctrl {
   uint64_t full[kMaxSlots];    // producer -> consumers: chunk landed (tx-count barrier)
   uint64_t empty[kMaxSlots];   // consumers -> producer: slot free again (16 warp arrivals)
-  uint64_t cbar;               // cluster barrier (ar_decode.cu): one arrival per CTA of the cluster per phase
+  uint64_t cbar;               // ar_decode.cu: the head's context rows of all 4 CTAs have landed (st.async transaction count)
+  uint64_t qbar;               // ar_decode.cu: q and the new K/V rows of this CTA's attention rows have landed
   float scratch[32];
   volatile int abort_flag;     // a wait timed out somewhere: fall through everything
   volatile int stop_flag;      // consumers are done (normal end or early exit)

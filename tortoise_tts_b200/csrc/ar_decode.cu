@@ -55,6 +55,18 @@ constexpr int kStageOffLn2 = 4096;
 constexpr int kXredOffsetFloats = 4096;
 constexpr int kRinfoOffsetFloats = 6144;
 constexpr int kCtxOffsetFloats = 7168;
+// MODE 1 / 2 (<= 4 attention rows per CTA): q and the new position's K / V rows of a CTA's attention rows arrive in its shared
+// memory (st.async from the 4 c_attn epilogues of the cluster) instead of through global memory behind a release fence
+constexpr int kKvNewOffsetFloats = 7680;   // bf16 [K | V][attention row][64]  (after the 2 KiB context tile of MODE 1 / 2)
+constexpr int kQsOffsetFloats = 8192;      // fp32 [attention row][64]
+template <int MODE>
+struct QkvAsync {
+#ifdef TTS_QKV_SYNC
+  static constexpr bool on = false;
+#else
+  static constexpr bool on = MODE <= 2;    // MODE 4 has no shared memory left for the 4 KiB it would need
+#endif
+};
 
 // ---- hardware cluster barrier (all 256 threads of the 4 CTAs; ~0.2 us).  release/acquire at cluster scope: global
 // and distributed-shared writes made before it are visible to the cluster's threads after it. -----------------------
@@ -306,8 +318,10 @@ struct Gran {
   int cnt;
 };
 
+// pnew >= 0 (last private granule only, MODE 1 / 2): index in the granule of the position written by THIS layer's c_attn;
+// its K / V (8 dims of this lane: knew / vnew) are taken from shared memory, the pool copy is for the steps to come
 __device__ __forceinline__ void gran_load(Gran& G, const __nv_bfloat16* kvb, const int* pt, int g, int Gp, int plen, int len,
-                                          int rg) {
+                                          int rg, int pnew = -1, const uint4* knew = nullptr, const uint4* vnew = nullptr) {
   int pos0, cnt, page;
   if (g < Gp) {
     pos0 = 16 * g;
@@ -324,12 +338,12 @@ __device__ __forceinline__ void gran_load(Gran& G, const __nv_bfloat16* kvb, con
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     const int r = 4 * j + rg;
-    G.k[j] = (r < cnt) ? ld_cg_u4(kb + r * kHD) : make_uint4(0u, 0u, 0u, 0u);
+    G.k[j] = (r < cnt) ? (r == pnew ? *knew : ld_cg_u4(kb + r * kHD)) : make_uint4(0u, 0u, 0u, 0u);
   }
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     const int r = 4 * j + rg;
-    G.v[j] = (r < cnt) ? ld_cg_u4(vb + r * kHD) : make_uint4(0u, 0u, 0u, 0u);
+    G.v[j] = (r < cnt) ? (r == pnew ? *vnew : ld_cg_u4(vb + r * kHD)) : make_uint4(0u, 0u, 0u, 0u);
   }
 }
 
@@ -427,13 +441,24 @@ __device__ void attn_local(const Params& P, int layer, int head, int attn_row0, 
 #endif
         constexpr int NG = TTS_ATTN_DEPTH;             // granules in flight per warp (4 KiB each), a register ring
         Gran G[NG];
+        // the granule that holds the position this layer's c_attn has just produced (always the last private one)
+        const int g_new = QkvAsync<MODE>::on ? Gt - 1 : -2, p_new = (len - 1 - plen) & 15;
+        const uint4* knew = reinterpret_cast<const uint4*>(sm.red + kKvNewOffsetFloats) + j * 8 + dc;
+        const uint4* vnew = knew + C::kAttnRows * 8;
+        auto load = [&](Gran& Gx, int g) { gran_load(Gx, kvb, pt, g, Gp, plen, len, rg, g == g_new ? p_new : -1, knew, vnew); };
 #pragma unroll
         for (int i = 0; i < NG - 1; ++i)
-          if (g0 + i < g1) gran_load(G[i], kvb, pt, g0 + i, Gp, plen, len, rg);
+          if (g0 + i < g1) load(G[i], g0 + i);
         float qv[8];
         {
-          const float* qp = P.q + (size_t)row * kD + head * kHD + dc * 8;
-          const float4 a = ld_cg_f4(qp), b = ld_cg_f4(qp + 4);
+          float4 a, b;
+          if (QkvAsync<MODE>::on) {
+            const float4* qs = reinterpret_cast<const float4*>(sm.red + kQsOffsetFloats + j * kHD + dc * 8);
+            a = qs[0]; b = qs[1];
+          } else {
+            const float* qp = P.q + (size_t)row * kD + head * kHD + dc * 8;
+            a = ld_cg_f4(qp); b = ld_cg_f4(qp + 4);
+          }
           qv[0] = a.x * kLog2e; qv[1] = a.y * kLog2e; qv[2] = a.z * kLog2e; qv[3] = a.w * kLog2e;
           qv[4] = b.x * kLog2e; qv[5] = b.y * kLog2e; qv[6] = b.z * kLog2e; qv[7] = b.w * kLog2e;
         }
@@ -442,7 +467,7 @@ __device__ void attn_local(const Params& P, int layer, int head, int attn_row0, 
 #pragma unroll
           for (int k = 0; k < NG; ++k) {
             if (g + k < g1) {
-              if (g + k + NG - 1 < g1) gran_load(G[(k + NG - 1) % NG], kvb, pt, g + k + NG - 1, Gp, plen, len, rg);
+              if (g + k + NG - 1 < g1) load(G[(k + NG - 1) % NG], g + k + NG - 1);
               if (QPW > 1) while (g + k >= qend) { flush(); qend = ((q + 1) * Gt) >> 2; }
               gran_reduce(G[k], qv, rg, m, l, acc);
             }
@@ -478,9 +503,19 @@ __device__ void attn_local(const Params& P, int layer, int head, int attn_row0, 
     // the split-K c_proj of all 4 CTAs reads this row: push the pair into everyone's copy
     __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(ctx_smem(sm)) + afrag_elem_offset(ctx_row0 + w, 2 * lane, kHD);
     const uint32_t pk = pack_bf16x2(o0, o1);
+#ifndef TTS_CTX_SYNC
+    // every store completes 4 bytes on the receiver's context barrier (armed by its thread 0 below): the split-K c_proj waits
+    // for that barrier instead of a cluster barrier behind a release fence
+#pragma unroll
+    for (int d = 0; d < kClusterSize; ++d) st_async_u32(dst, d, pk, &sm.ctrl->cbar);
+#else
 #pragma unroll
     for (int d = 0; d < kClusterSize; ++d) st_cluster_u32(dst, d, pk);
+#endif
   }
+#ifndef TTS_CTX_SYNC
+  if (threadIdx.x == 0) mbar_arrive_expect_tx(&sm.ctrl->cbar, kClusterSize * C::kAttnRows * kHD * 2);
+#endif
   prof_mark(P, sm.ctrl, 13);
 }
 
@@ -859,6 +894,8 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
   tile_range(P.v_tiles, P.G, 0, blockIdx.x, &fd.ht0, &fd.hcnt);
   if (threadIdx.x == 0) {
     for (int i = 0; i < P.n_slots; ++i) mbar_init(&c->full[i], 1);
+    mbar_init(&c->cbar, 1);
+    mbar_init(&c->qbar, 1);
     c->abort_flag = 0;
     c->ibuf[0] = 0;
     c->ibuf[1] = 0;
@@ -874,6 +911,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
   Pipe pipe;
   pipe.ci = 0; pipe.slot = 0; pipe.phase = 0; pipe.n_slots = P.n_slots;
   uint32_t epoch = 0;
+  uint32_t ctx_phase = 0, q_phase = 0;
   int steps_done = 0;
   bool alive = true;
   const int n = P.n_rows;
@@ -935,6 +973,8 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       cluster_barrier_at<1>();
       prof_mark(P, c, 1);
       if (is_head) break;
+      if (QkvAsync<MODE>::on && threadIdx.x == 0)      // q (256 B) + new K + new V (128 B each) per attention row
+        mbar_arrive_expect_tx(&c->qbar, C::kAttnRows * (kHD * 4 + 2 * kHD * 2));
       {
         const float* bias = layer_f(P, layer) + kFOffBqkv;
         const int* ri = rinfo_ptr(sm);
@@ -942,8 +982,19 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
         gemm16<6, C::kMtA, C::kHalf, false>(P, sm, pipe, fd, 6, row_lo, bias, true, [&](int i) { return t0 + (i >> 1) * (kD / 8) + (i & 1); },
                         [&](int lrow, int col, float v0, float v1) {
                           const int row = tile_row0 + lrow;
-                          if (row >= n) return;
                           const int part = col >> 10, cc = col & (kD - 1);
+                          if (QkvAsync<MODE>::on) {
+                            // to the CTA that attends this row, ALWAYS (its barrier counts bytes, also for rows past the end)
+                            const int rel = row - row_lo, dst = rel / C::kAttnRows, j = rel - dst * C::kAttnRows, d = cc & (kHD - 1);
+                            if (part == 0) {
+                              st_async_u2(sm.red + kQsOffsetFloats + j * kHD + d, (uint32_t)dst,
+                                          make_uint2(__float_as_uint(v0 * 0.125f), __float_as_uint(v1 * 0.125f)), &c->qbar);
+                            } else {
+                              __nv_bfloat16* kvs = reinterpret_cast<__nv_bfloat16*>(sm.red + kKvNewOffsetFloats);
+                              st_async_u32(kvs + ((part - 1) * C::kAttnRows + j) * kHD + d, (uint32_t)dst, pack_bf16x2(v0, v1), &c->qbar);
+                            }
+                          }
+                          if (row >= n) return;
                           if (part == 0) {   // query, pre-scaled by 1/sqrt(64) (exact: power of two)
                             *reinterpret_cast<float2*>(P.q + (size_t)row * kD + cc) = make_float2(v0 * 0.125f, v1 * 0.125f);
                           } else {           // key / value -> page slot of this row's new position (row facts of the step)
@@ -954,10 +1005,28 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
                           }
                         });
       }
-      cluster_barrier_at<2>();
+      if (QkvAsync<MODE>::on) {
+        if (!mbar_wait(&c->qbar, q_phase, &c->abort_flag)) {
+          *reinterpret_cast<volatile int*>(P.watchdog) = 1;
+          alive = false;
+          break;
+        }
+        q_phase ^= 1u;
+      } else {
+        cluster_barrier_at<2>();
+      }
       prof_mark(P, c, 200 + OP_ATTN);
       attn_local<MODE>(P, layer, head, attn_row0, ctx_row0, sm);
+#ifndef TTS_CTX_SYNC
+      if (!mbar_wait(&c->cbar, ctx_phase, &c->abort_flag)) {
+        *reinterpret_cast<volatile int*>(P.watchdog) = 1;
+        alive = false;
+        break;
+      }
+      ctx_phase ^= 1u;
+#else
       cluster_barrier_at<4>();
+#endif
       prof_mark(P, c, 200 + OP_PROJ);
       proj_splitk<MODE>(P, rank, row_lo, tile_row0, sm, pipe);
       // ---- phase B: ln_2 -> c_fc -> gelu_new ----

@@ -132,6 +132,26 @@ __device__ __forceinline__ void st_cluster_u2(void* local_ptr, uint32_t rank, ui
       "r"(rank), "r"(v.x), "r"(v.y)
       : "memory");
 }
+// 4-byte store into the shared memory of CTA `rank` that completes 4 bytes of the transaction count of the mbarrier at
+// `local_bar`'s offset in the SAME CTA: the receiver waits on its own barrier, the sender needs no fence and no cluster barrier
+__device__ __forceinline__ void st_async_u32(void* local_ptr, uint32_t rank, uint32_t v, uint64_t* local_bar) {
+  asm volatile(
+      "{\n\t.reg .b32 ra, rb;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mapa.shared::cluster.u32 rb, %3, %1;\n\t"
+      "st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [ra], %2, [rb];\n\t}" ::"r"(smem_u32(local_ptr)),
+      "r"(rank), "r"(v), "r"(smem_u32(local_bar))
+      : "memory");
+}
+__device__ __forceinline__ void st_async_u2(void* local_ptr, uint32_t rank, uint2 v, uint64_t* local_bar) {
+  asm volatile(
+      "{\n\t.reg .b32 ra, rb;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mapa.shared::cluster.u32 rb, %4, %1;\n\t"
+      "st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.b32 [ra], {%2, %3}, [rb];\n\t}" ::"r"(smem_u32(local_ptr)),
+      "r"(rank), "r"(v.x), "r"(v.y), "r"(smem_u32(local_bar))
+      : "memory");
+}
 __device__ __forceinline__ void st_cluster_u32(void* local_ptr, uint32_t rank, uint32_t v) {
   asm volatile(
       "{\n\t.reg .b32 ra;\n\t"
