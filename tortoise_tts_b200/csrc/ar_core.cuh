@@ -14,6 +14,7 @@ struct Ctrl {
   uint64_t empty[kMaxSlots];   // consumers -> producer: slot free again (16 warp arrivals)
   uint64_t cbar;               // ar_decode.cu: the head's context rows of all 4 CTAs have landed (st.async transaction count)
   uint64_t qbar;               // ar_decode.cu: q and the new K/V rows of this CTA's attention rows have landed
+  uint64_t xbar[2];            // ar_decode.cu: the 4 K-partials of this CTA's mlp.c_proj tile have landed (row groups alternate)
   float scratch[32];
   volatile int abort_flag;     // a wait timed out somewhere: fall through everything
   volatile int stop_flag;      // consumers are done (normal end or early exit)

@@ -706,7 +706,8 @@ __device__ void proj_splitk(const Params& P, int rank, int row_lo, int tile_row0
 // 128 KiB: the SM's ~55 GB/s L2 read port is what this stage waits for).  The four K-partials of a tile are sent to the
 // tile's owner (rank t owns tile t) through distributed shared memory and summed there in rank order (deterministic).
 template <int MODE>
-__device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pipe, Feeder& fd, int rank, int grp, bool commit, uint32_t xtag) {
+__device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pipe, Feeder& fd, int rank, int grp, bool commit, uint32_t xtag,
+                            uint32_t& x_phase) {
   using C = DecCfg<MODE>;
   constexpr int MT = C::kMtB;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -774,10 +775,25 @@ __device__ void proj2_stage(const Params& P, int layer, const Smem& sm, Pipe& pi
       s0 += v.x;
       s1 += v.y;
     }
+#ifndef TTS_X_SYNC
+    // counted on the owner's barrier of this row group (st.async): no release fence, no cluster barrier.  A peer is at most one
+    // row group ahead (its next wait needs this CTA's next partials), so two alternating barriers keep the phases apart.
+    st_async_u2(xred + (mt * kClusterSize + rank) * 64 + rem, (uint32_t)t, make_uint2(__float_as_uint(s0), __float_as_uint(s1)), &c->xbar[grp & 1]);
+#else
     st_cluster_u2(xred + (mt * kClusterSize + rank) * 64 + rem, (uint32_t)t, make_uint2(__float_as_uint(s0), __float_as_uint(s1)));
+#endif
   }
   if (commit) fd.pending += 4;
+#ifndef TTS_X_SYNC
+  if (threadIdx.x == 0) mbar_arrive_expect_tx(&c->xbar[grp & 1], kClusterSize * MT * 64 * 8);
+  if (!mbar_wait(&c->xbar[grp & 1], (x_phase >> (grp & 1)) & 1u, &c->abort_flag)) {
+    *reinterpret_cast<volatile int*>(P.watchdog) = 1;
+    return;
+  }
+  x_phase ^= 1u << (grp & 1);
+#else
   cluster_barrier();
+#endif
   if (owner) {
     float s0 = 0.f, s1 = 0.f;
 #pragma unroll
@@ -896,6 +912,8 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
     for (int i = 0; i < P.n_slots; ++i) mbar_init(&c->full[i], 1);
     mbar_init(&c->cbar, 1);
     mbar_init(&c->qbar, 1);
+    mbar_init(&c->xbar[0], 1);
+    mbar_init(&c->xbar[1], 1);
     c->abort_flag = 0;
     c->ibuf[0] = 0;
     c->ibuf[1] = 0;
@@ -911,7 +929,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
   Pipe pipe;
   pipe.ci = 0; pipe.slot = 0; pipe.phase = 0; pipe.n_slots = P.n_slots;
   uint32_t epoch = 0;
-  uint32_t ctx_phase = 0, q_phase = 0;
+  uint32_t ctx_phase = 0, q_phase = 0, x_phase = 0;
   int steps_done = 0;
   bool alive = true;
   const int n = P.n_rows;
@@ -1058,7 +1076,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
       if (!alive) break;
       prof_mark(P, c, 200 + OP_PROJ2);
 #pragma unroll 1
-      for (int grp = 0; grp < C::kGroups; ++grp) proj2_stage<MODE>(P, layer, sm, pipe, fd, rank, grp, grp == C::kGroups - 1, xtag + 1);
+      for (int grp = 0; grp < C::kGroups; ++grp) proj2_stage<MODE>(P, layer, sm, pipe, fd, rank, grp, grp == C::kGroups - 1, xtag + 1, x_phase);
       if (c->abort_flag) alive = false;
     }
     if (!alive) break;
