@@ -4,7 +4,7 @@
 mkdir -p gpurun_out
 B="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-sub-configs"
 timeout 600 $B > gpurun_out/plain.log 2>&1 && \
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r02_launches.csv $B > gpurun_out/ncu_list.log 2>&1
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/r02_launches.csv $B > gpurun_out/ncu_list.log 2>&1
 tail -2 gpurun_out/ncu_list.log
 export TTS_BENCH_MAX_NEW=120
 timeout 600 $B > gpurun_out/plain2.log 2>&1 && \
