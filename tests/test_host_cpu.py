@@ -43,6 +43,9 @@ def test_product_fails_loudly_without_a_gpu(built):
         UnifiedVoiceB200({}, device="cpu")
     with pytest.raises(RuntimeError):
         UnifiedVoiceB200({}, device="cuda:0")
+    from tortoise_tts_b200.clvp import CLVPB200
+    with pytest.raises(RuntimeError):
+        CLVPB200({}, depth=1)
 
 
 def test_product_does_not_import_the_oracle():
@@ -135,14 +138,18 @@ _WORKER = r'''
 import os, sys, torch, torch.distributed as dist
 sys.path.insert(0, sys.argv[1])
 from tortoise_tts_b200.shard import plan_shards, gather_codes
-dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%s" % sys.argv[2], rank=int(sys.argv[3]), world_size=2)
+backend = sys.argv[4] if len(sys.argv) > 4 else "gloo"
+dev = torch.device("cuda", int(sys.argv[3])) if backend == "nccl" else torch.device("cpu")
+if backend == "nccl":
+    torch.cuda.set_device(dev)
+dist.init_process_group(backend, init_method="tcp://127.0.0.1:%s" % sys.argv[2], rank=int(sys.argv[3]), world_size=2)
 rank = dist.get_rank()
 for (U, N) in ((1, 6), (3, 2)):
     shards = plan_shards(U, N, 2)
     me = shards[rank]
     steps = 4 + rank                                  # ranks stop at different lengths
     g = torch.tensor(me.global_indices())
-    codes = (g[:, None] * 100 + torch.arange(steps)[None]).long()
+    codes = (g[:, None] * 100 + torch.arange(steps)[None]).long().to(dev)
     lat = codes[..., None].float().repeat(1, 1, 3)
     out, out_lat = gather_codes(codes, 8193, shards, latents=lat)
     assert out.shape == (U * N, 5), out.shape
@@ -158,7 +165,7 @@ print("ok", rank)
 '''
 
 
-def test_gather_codes_world2_gloo(tmp_path):
+def run_world2(tmp_path, backend):
     import socket
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -166,12 +173,24 @@ def test_gather_codes_world2_gloo(tmp_path):
     s.close()
     script = tmp_path / "w.py"
     script.write_text(_WORKER)
-    procs = [subprocess.Popen([sys.executable, str(script), ROOT, str(port), str(r)], stdout=subprocess.PIPE,
+    procs = [subprocess.Popen([sys.executable, str(script), ROOT, str(port), str(r), backend], stdout=subprocess.PIPE,
                               stderr=subprocess.STDOUT, text=True) for r in range(2)]
     outs = [p.communicate(timeout=240)[0] for p in procs]
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
         assert "ok" in o
+
+
+def test_gather_codes_world2_gloo(tmp_path):
+    run_world2(tmp_path, "gloo")
+
+
+@pytest.mark.gpu
+def test_gather_codes_world2_nccl(tmp_path):
+    """The same two-rank gather over NCCL on two GPUs (skipped on a one-GPU box; run with `gpurun --gpus 2`)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    run_world2(tmp_path, "nccl")
 
 
 # ---- the device sampler's threshold search, restated in numpy (csrc/ar_sample.cuh) ---------------------------------
