@@ -253,6 +253,15 @@ typedef struct {
 } TtsArCondWeights;
 
 int tts_ar_load_conditioning_weights(TtsArHandle* h, const TtsArCondWeights* w, void* stream);
+/* The mel-spectrogram front end of the same row: TorchMelSpectrogram.forward (reference tortoise_tts/models/arch_utils.py:361-395,
+ * called by tortoise_tts/emb/mel.py:50-65) = torchaudio MelSpectrogram(n_fft 1024, hop 256, Hann, power 2, centre / reflect padding,
+ * 80 HTK-scale slaney-normalised filters over 0..8000 Hz at 22050 Hz), log(clamp(., 1e-5)), / mel_norms.  One CTA per frame: a
+ * 1024-point DFT against a sine / cosine table in shared memory with fp64 accumulation, the filter bank and the logarithm fused.
+ *   wav    dev float32 [n_wav, n_samples] (n_samples > 512);  mel_norms dev float32 [80] or NULL
+ *   mel    dev float32 [n_wav, 80, 1 + n_samples / 256]
+ * ASYNC on `stream`; the first call on a handle allocates and fills the 0.2 MB of tables (SYNC once). */
+int tts_ar_mel_spectrogram(TtsArHandle* h, const float* wav, int32_t n_wav, int32_t n_samples, const float* mel_norms, float* mel,
+                           void* stream);
 /*   mel     dev float32 [n_clips, spec_dim, frames]  (speech_conditioning_input[b] of the reference)
  *   latent  dev float32 [1024]: mean over the clips of column 0 of the encoder output.  ASYNC on `stream`. */
 int tts_ar_get_conditioning(TtsArHandle* h, const float* mel, int32_t n_clips, int32_t frames, float* latent, void* stream);
@@ -318,6 +327,9 @@ int tts_ar_clvp_load_weights(TtsClvpHandle* h, const TtsClvpWeights* w, void* st
 int tts_ar_clvp_score(TtsClvpHandle* h, const int32_t* text, int32_t n_text, int32_t text_len, int32_t text_stride,
                       const int64_t* codes, int32_t n, int32_t codes_len, int32_t codes_stride, float* scores,
                       float* speech_latents, void* stream);
+/* indices[r] (dev int64 [k]) = the candidate with the r-th largest score: `torch.topk(scores, k=candidates).indices` of
+ * reference inference.py:395 without leaving the device (ties: lower index first; scores must not be NaN).  ASYNC. */
+int tts_ar_clvp_topk(TtsClvpHandle* h, const float* scores, int32_t n, int32_t k, int64_t* indices, void* stream);
 /* Waits for `stream`; TTS_AR_ERR_BAD_ARG after an out-of-range token id, TTS_AR_ERR_WATCHDOG after a device-side time-out
  * (each reported once and cleared).  *launches (nullable) = this library's kernel launches on the handle so far.  SYNC. */
 int tts_ar_clvp_sync(TtsClvpHandle* h, int64_t* launches, void* stream);

@@ -116,6 +116,10 @@ def test_clvp_full_size_candidates_are_scored_independently(clvp_cls):
     s_perm = m(text.cuda(), codes[perm].cuda())
     assert torch.isfinite(scores).all()
     assert torch.equal(s_perm, scores[perm.cuda()])
+    for k in (1, 4, 16):                              # inference.py:395: indices = torch.topk(scores, k=candidates).indices
+        assert m.topk(scores, k).tolist() == torch.topk(scores, k).indices.tolist()
+    with pytest.raises(ValueError):
+        m.topk(scores, 17)
     sub = m(text.cuda(), codes[[3, 12]].cuda())
     assert torch.equal(sub, scores[[3, 12]])
     want = OracleCLVP(sd, cfg).score(text, codes[[3, 12]])

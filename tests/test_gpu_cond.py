@@ -85,3 +85,32 @@ def test_conditioning_vs_oracle_shapes_and_use_as_prompt():
     codes2 = m.inference_speech(lat, text, num_return_sequences=2, max_generate_length=12, do_sample=False, ignore_eos=True)
     assert codes.shape == (2, 12) and torch.equal(codes, codes2)
     m.close()
+
+
+@pytest.mark.parametrize("case", ["short", "clip"])
+def test_mel_spectrogram_matches_the_reference_goldens(golden_dir, case):
+    """tts_ar_mel_spectrogram against the reference's TorchMelSpectrogram outputs (tests/golden/mel.npz): fp32 path (direct DFT
+    with fp64 accumulation), so the bar is the fp32 one of BASELINE.json (1e-4 relative); then wav -> mel -> latent end to end
+    against the two oracles chained."""
+    from oracle.mel_oracle import make_wav, oracle_mel
+    g = np.load(os.path.join(golden_dir, "mel.npz"))
+    spec = ast.literal_eval(str(g[f"{case}_spec"]))
+    norms = torch.from_numpy(g["mel_norms"])
+    wav = make_wav(spec["batch"], spec["samples"], seed=spec["seed"])
+    m, cfg, sd = build_model(43, max_text_len=16, max_new_tokens=600)
+    mel = m.mel_spectrogram(wav.unsqueeze(1).cuda(), norms)
+    want = torch.from_numpy(g[f"{case}_mel"])
+    got = mel.cpu()[:, :, ::8] if case == "clip" else mel.cpu()
+    e = rel(got, want)
+    PARITY[f"mel/{case}"] = dict(mel_rel=e)
+    print(f"mel {case}: rel vs reference {e:.3e}")
+    assert got.shape == want.shape and e < 1e-4
+    assert rel(m.mel_spectrogram(wav.cuda()), oracle_mel(wav)) < 1e-4          # no norms, [b, n] input form
+    lat = m.get_conditioning(mel[:, None])                                       # emb/mel.py:92-97: [b, 1, 80, frames]
+    want_lat = OracleConditioning(sd).get_conditioning(oracle_mel(wav, norms)[:, None])
+    e2 = rel(lat, want_lat)
+    PARITY[f"mel/{case}"]["latent_from_wav_rel"] = e2
+    assert e2 < BF16_REL
+    with pytest.raises(ValueError):
+        m.mel_spectrogram(torch.zeros(1, 400).cuda())
+    m.close()

@@ -211,3 +211,18 @@ def test_conditioning_oracle_matches_the_reference_class(golden_dir, case):
     want = torch.from_numpy(g[f"{case}_latent"])
     assert lat.shape == want.shape == (spec["batch"], 1024)
     assert rel(lat.numpy(), want.numpy()) < FP32_REL
+
+
+# ---- mel-spectrogram front end: oracle/mel_oracle.py vs the reference's TorchMelSpectrogram ---------
+@pytest.mark.parametrize("case", ["short", "clip"])
+def test_mel_oracle_matches_the_reference_class(golden_dir, case):
+    import ast
+    from oracle.mel_oracle import make_wav, oracle_mel
+    g = np.load(os.path.join(golden_dir, "mel.npz"))
+    spec = ast.literal_eval(str(g[f"{case}_spec"]))
+    mel = oracle_mel(make_wav(spec["batch"], spec["samples"], seed=spec["seed"]), torch.from_numpy(g["mel_norms"]))
+    want = torch.from_numpy(g[f"{case}_mel"])
+    if case == "clip":
+        assert mel.shape[-1] == 517                      # 132300 samples = the reference's conditioning clip (emb/mel.py:50)
+        mel = mel[:, :, ::8]
+    assert (mel - want).abs().max() < 1e-5

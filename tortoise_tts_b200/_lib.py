@@ -16,7 +16,7 @@ SYMBOLS = [
     "tts_ar_debug_gemm", "tts_ar_set_option", "tts_ar_stream_begin", "tts_ar_stream_poll", "tts_ar_stream_end",
     "tts_ar_gemm_f32_noalloc",
     "tts_ar_clvp_create", "tts_ar_clvp_destroy", "tts_ar_clvp_last_error", "tts_ar_clvp_load_weights", "tts_ar_clvp_score",
-    "tts_ar_clvp_sync", "tts_ar_load_conditioning_weights", "tts_ar_get_conditioning",
+    "tts_ar_clvp_sync", "tts_ar_clvp_topk", "tts_ar_load_conditioning_weights", "tts_ar_get_conditioning", "tts_ar_mel_spectrogram",
 ]
 
 ABI_VERSION = 2
@@ -120,6 +120,7 @@ def load():
     lib.tts_ar_gemm_f32_noalloc.argtypes = [f32p, vp, f32p, f32p, i32, i32, i32, i32, i32p, vp]
     lib.tts_ar_load_conditioning_weights.argtypes = [vp, C.POINTER(TtsArCondWeights), vp]
     lib.tts_ar_get_conditioning.argtypes = [vp, f32p, i32, i32, f32p, vp]
+    lib.tts_ar_mel_spectrogram.argtypes = [vp, f32p, i32, i32, f32p, f32p, vp]
     lib.tts_ar_clvp_create.argtypes = [C.POINTER(TtsClvpConfig), C.POINTER(vp)]
     lib.tts_ar_clvp_destroy.argtypes = [vp]
     lib.tts_ar_clvp_destroy.restype = None
@@ -127,6 +128,7 @@ def load():
     lib.tts_ar_clvp_last_error.restype = C.c_char_p
     lib.tts_ar_clvp_load_weights.argtypes = [vp, C.POINTER(TtsClvpWeights), vp]
     lib.tts_ar_clvp_score.argtypes = [vp, i32p, i32, i32, i32, i64p, i32, i32, i32, f32p, f32p, vp]
+    lib.tts_ar_clvp_topk.argtypes = [vp, f32p, i32, i32, i64p, vp]
     lib.tts_ar_clvp_sync.argtypes = [vp, C.POINTER(C.c_int64), vp]
     lib.tts_ar_set_option.argtypes = [vp, C.c_char_p, i32]
     lib.tts_ar_stream_begin.argtypes = [vp, C.POINTER(TtsArSampling), i32, i64p, f32p, vp]

@@ -128,6 +128,15 @@ class CLVPB200:
 
     __call__ = forward
 
+    def topk(self, scores, k):
+        """`torch.topk(scores, k=k).indices` (reference inference.py:395) on the device: int64 [k], best first."""
+        scores = scores.to(device=self.device, dtype=torch.float32).contiguous()
+        out = torch.empty(int(k), dtype=torch.int64, device=self.device)
+        with torch.cuda.device(self.device):
+            self._check(self.lib.tts_ar_clvp_topk(self.handle, _ptr(scores), scores.numel(), int(k), _ptr(out), self._stream()),
+                        "tts_ar_clvp_topk")
+        return out
+
     def eval(self):
         return self
 

@@ -161,6 +161,20 @@ __global__ void __launch_bounds__(256) clvp_score_kernel(const float* __restrict
   if (lane == 0) scores[i] = d * expf(temperature[0]);
 }
 
+// indices[r] = the candidate with the r-th largest score, r < k (torch.topk(scores, k).indices of reference inference.py:395; ties:
+// the lower index first).  Rank by counting -- n is a candidate count (<= 4096), one CTA.
+__global__ void __launch_bounds__(256) clvp_topk_kernel(const float* __restrict__ scores, int n, int k, long long* __restrict__ indices) {
+  for (int i = threadIdx.x; i < n; i += 256) {
+    const float si = scores[i];
+    int rank = 0;
+    for (int j = 0; j < n; ++j) {
+      const float sj = scores[j];
+      rank += (sj > si || (sj == si && j < i)) ? 1 : 0;
+    }
+    if (rank < k) indices[rank] = i;
+  }
+}
+
 // ---- GLU weight image: rows interleaved per 32 hidden units -----------------------------------------------------------------
 // src nn.Linear [3072][768]: rows [0,1536) = value, [1536,3072) = gate (GLU.forward: proj(x).chunk(2), xtransformers.py:438).
 // dst row (u / 32) * 64 + (u % 32) = value row u, + 32 = gate row u, so that one 64-column slice of an output tile holds both
@@ -448,6 +462,18 @@ extern "C" int tts_ar_clvp_score(TtsClvpHandle* h, const int32_t* text, int32_t 
   h->launches += 1;
   e = cudaGetLastError();
   if (e != cudaSuccess) return ccuda(h, e, "clvp_score_kernel launch");
+  return 0;
+}
+
+extern "C" int tts_ar_clvp_topk(TtsClvpHandle* h, const float* scores, int32_t n, int32_t k, int64_t* indices, void* stream) {
+  if (!h || !scores || !indices) return cfail(h, TTS_AR_ERR_BAD_ARG, "null argument");
+  if (n < 1 || n > 4096 || k < 1 || k > n) return cfail(h, TTS_AR_ERR_BAD_ARG, "clvp_topk: need 1 <= k <= n <= 4096");
+  cudaError_t e = cudaSetDevice(h->cfg.device);
+  if (e != cudaSuccess) return ccuda(h, e, "cudaSetDevice");
+  clvp_topk_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(scores, n, k, reinterpret_cast<long long*>(indices));
+  h->launches += 1;
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return ccuda(h, e, "clvp_topk_kernel launch");
   return 0;
 }
 

@@ -8,8 +8,10 @@
 //     (-> bf16 A operand) -> qkv GEMM (tcgen05, rows reordered to q | k | v at load) -> full_attn_kernel<1024> ->
 //     proj_out GEMM (+bias, +residual) -> cond_take_kernel (row 0, running mean over the clips)
 // Uses the AR handle's activation buffers (x, xn, ctx, h) and its A-operand tensor maps (dense_pass.cu).
+#include <cmath>
 #include <cstdio>
 #include <string>
+#include <vector>
 #include "tc_launch.cuh"
 #include "full_attn.cuh"
 #include "tts_ar_host.h"
@@ -119,6 +121,48 @@ template <typename T>
 __global__ void __launch_bounds__(256) cond_pack_init_kernel(const T* __restrict__ w, float* __restrict__ wt, int spec_dim) {
   const int k = blockIdx.x;
   for (int c = threadIdx.x; c < kD; c += 256) wt[(size_t)k * kD + c] = (float)w[(size_t)c * spec_dim + k];
+}
+
+// ---- mel-spectrogram front end (TorchMelSpectrogram.forward, arch_utils.py:361-395) --------------------------------------------
+constexpr int kMelFft = 1024, kMelHop = 256, kMelBins = kMelFft / 2 + 1, kMelN = 80;
+
+// One CTA per (frame, clip): windowed frame (centre padding of 512 samples each side, reflected) -> 513-bin power spectrum by a
+// direct DFT against the cos | sin table (index (k * j) mod 1024, fp64 accumulation) -> 80 mel filters -> log(clamp) / norm.
+__global__ void __launch_bounds__(256) mel_frames_kernel(const float* __restrict__ wav, int n, const float* __restrict__ win,
+                                                         const double* __restrict__ tw, const float* __restrict__ fb,
+                                                         const float* __restrict__ norms, float* __restrict__ mel, int frames) {
+  __shared__ double cs[kMelFft], sn[kMelFft];
+  __shared__ float x[kMelFft], pw[kMelBins + 3];
+  const int f = blockIdx.x, clip = blockIdx.y;
+  const float* w = wav + (size_t)clip * n;
+  for (int j = threadIdx.x; j < kMelFft; j += 256) {
+    int i = f * kMelHop + j - kMelFft / 2;
+    if (i < 0) i = -i;
+    if (i >= n) i = 2 * (n - 1) - i;
+    x[j] = w[i] * win[j];
+    cs[j] = tw[j];
+    sn[j] = tw[kMelFft + j];
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < kMelBins; k += 256) {
+    double re = 0.0, im = 0.0;
+#pragma unroll 4
+    for (int j = 0; j < kMelFft; ++j) {
+      const int idx = (k * j) & (kMelFft - 1);
+      re += (double)x[j] * cs[idx];
+      im += (double)x[j] * sn[idx];
+    }
+    pw[k] = (float)(re * re + im * im);
+  }
+  __syncthreads();
+  if (threadIdx.x < kMelN) {
+    const int m = threadIdx.x;
+    float acc = 0.f;
+    for (int k = 0; k < kMelBins; ++k) acc = fmaf(pw[k], fb[k * kMelN + m], acc);
+    float v = logf(fmaxf(acc, 1e-5f));
+    if (norms) v /= norms[m];
+    mel[((size_t)clip * kMelN + m) * frames + f] = v;
+  }
 }
 
 }  // namespace tts
@@ -240,5 +284,56 @@ extern "C" int tts_ar_get_conditioning(TtsArHandle* h, const float* mel, int32_t
   if (e != cudaSuccess) return cuda_fail(h, e, "conditioning encoder kernel launch");
   e = cudaGetLastError();
   if (e != cudaSuccess) return cuda_fail(h, e, "conditioning encoder");
+  return 0;
+}
+
+static int mel_tables(TtsArHandle* h) {
+  CondW& c = h->cond;
+  if (c.mel_fb) return 0;
+  std::vector<float> win(kMelFft), fb((size_t)kMelBins * kMelN);
+  std::vector<double> tw(2 * kMelFft);
+  const double two_pi = 6.283185307179586476925286766559;
+  for (int j = 0; j < kMelFft; ++j) {
+    win[j] = (float)(0.5 - 0.5 * cos(two_pi * j / kMelFft));          // periodic Hann (torch.hann_window default)
+    tw[j] = cos(two_pi * j / kMelFft);
+    tw[kMelFft + j] = sin(two_pi * j / kMelFft);
+  }
+  // torchaudio.functional.melscale_fbanks(513, 0, 8000, 80, 22050, norm="slaney", mel_scale="htk")
+  const double sr = 22050.0, f_max = 8000.0, m_max = 2595.0 * log10(1.0 + f_max / 700.0);
+  std::vector<double> fp(kMelN + 2);
+  for (int i = 0; i < kMelN + 2; ++i) fp[i] = 700.0 * (pow(10.0, (m_max * i / (kMelN + 1)) / 2595.0) - 1.0);
+  for (int k = 0; k < kMelBins; ++k) {
+    const double fr = (double)((int)sr / 2) * k / (kMelBins - 1);
+    for (int m = 0; m < kMelN; ++m) {
+      const double down = (fr - fp[m]) / (fp[m + 1] - fp[m]), up = (fp[m + 2] - fr) / (fp[m + 2] - fp[m + 1]);
+      const double tri = std::max(0.0, std::min(down, up));
+      fb[(size_t)k * kMelN + m] = (float)(tri * 2.0 / (fp[m + 2] - fp[m]));
+    }
+  }
+  int rc;
+  if ((rc = cond_alloc(h, &c.mel_win, win.size())) || (rc = cond_alloc(h, &c.mel_tw, tw.size()))) return rc;
+  float* fbp = nullptr;
+  if ((rc = cond_alloc(h, &fbp, fb.size()))) return rc;
+  TTS_CUDA(h, cudaMemcpy(c.mel_win, win.data(), win.size() * sizeof(float), cudaMemcpyHostToDevice));
+  TTS_CUDA(h, cudaMemcpy(c.mel_tw, tw.data(), tw.size() * sizeof(double), cudaMemcpyHostToDevice));
+  TTS_CUDA(h, cudaMemcpy(fbp, fb.data(), fb.size() * sizeof(float), cudaMemcpyHostToDevice));
+  c.mel_fb = fbp;
+  return 0;
+}
+
+extern "C" int tts_ar_mel_spectrogram(TtsArHandle* h, const float* wav, int32_t n_wav, int32_t n_samples, const float* mel_norms,
+                                      float* mel, void* stream) {
+  if (!h || !wav || !mel) return fail(h, TTS_AR_ERR_BAD_ARG, "null argument");
+  if (n_wav < 1 || n_wav > 65535 || n_samples <= kMelFft / 2)
+    return fail(h, TTS_AR_ERR_BAD_ARG, "mel_spectrogram: need 1..65535 clips of more than 512 samples (reflect padding)");
+  TTS_CUDA(h, cudaSetDevice(h->cfg.device));
+  const int rc = mel_tables(h);
+  if (rc) return rc;
+  const int frames = 1 + n_samples / kMelHop;
+  mel_frames_kernel<<<dim3(frames, n_wav), 256, 0, (cudaStream_t)stream>>>(wav, n_samples, h->cond.mel_win, h->cond.mel_tw, h->cond.mel_fb,
+                                                                           mel_norms, mel, frames);
+  h->launches += 1;
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(h, e, "mel_frames_kernel launch");
   return 0;
 }

@@ -29,6 +29,8 @@ struct CondW {
   int n_blocks = 0, spec_dim = 0;
   float *init_wt = nullptr, *init_b = nullptr;      // init conv, transposed [spec_dim][1024]; bias
   float* stats = nullptr;                           // GroupNorm (mean, rstd) per group [32][2]
+  float *mel_win = nullptr, *mel_fb = nullptr;      // mel front end: Hann window [1024], filters [513][80]
+  double* mel_tw = nullptr;                         // cos | sin of 2 pi i / 1024, [2][1024]
   struct Block {
     float *gn_w, *gn_b, *b_qkv, *b_proj;
     __nv_bfloat16 *qkv, *proj;                      // [3072][1024] rows reordered to q | k | v, [1024][1024]

@@ -191,6 +191,21 @@ class UnifiedVoiceB200:
         torch.cuda.synchronize(self.device)
         del keep
 
+    def mel_spectrogram(self, inp, mel_norms=None):
+        """TorchMelSpectrogram.forward (tortoise_tts/models/arch_utils.py:361-395): [b, n] or [b, 1, n] audio at 22.05 kHz ->
+        [b, 80, 1 + n // 256] normalised log-mel (what emb/mel.py:50-65 feeds to get_conditioning).  `mel_norms`: the 80 values
+        of the reference's data/models/mel_norms.pth (TorchMelSpectrogram.mel_norms), or None."""
+        x = inp.squeeze(1) if inp.dim() == 3 else inp
+        if x.dim() != 2:
+            raise ValueError("audio must be [b, n] or [b, 1, n]")
+        x = x.to(device=self.device, dtype=torch.float32).contiguous()
+        norms = None if mel_norms is None else mel_norms.to(device=self.device, dtype=torch.float32).contiguous()
+        out = torch.empty(x.shape[0], 80, 1 + x.shape[1] // 256, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            self._check(self.lib.tts_ar_mel_spectrogram(self.handle, _ptr(x), x.shape[0], x.shape[1], _ptr(norms), _ptr(out), self._stream()),
+                        "tts_ar_mel_spectrogram")
+        return out
+
     def get_conditioning(self, speech_conditioning_input):
         """UnifiedVoice.get_conditioning (unified_voice.py:535-542): [b, n_clips, 80, frames] (or [b, 80, frames]) mel
         spectrograms -> [b, 1024] conditioning latents (mean over the clips of column 0 of the conditioning encoder)."""
