@@ -69,21 +69,20 @@ __global__ void __launch_bounds__(256) clvp_rms_kernel(const float* __restrict__
 }
 
 // ---- tail: final LayerNorm of every row, mean over the sequence, to_latent, L2 normalise -------------------------------------
-// One CTA per sequence, 8 warps; warp w normalises rows w, w + 8, ... (two-pass statistics, eps 1e-5, biased variance as
-// F.layer_norm) and keeps a running sum; the 8 partial sums are added in warp order (deterministic).  Then
-// lat = W . mean (fp32 weights, one output per warp step, coalesced rows) and lat / max(||lat||, 1e-12) (F.normalize).
-__global__ void __launch_bounds__(256) clvp_pool_kernel(const float* __restrict__ x, const float* __restrict__ nw, const float* __restrict__ nb,
-                                                        const float* __restrict__ w_lat, float* __restrict__ lat_out, int len) {
+// Two kernels.  clvp_pool_partial_kernel: CTA (sequence, slice p of kPoolSlices): warp w normalises rows p + kPoolSlices (w + 8 i)
+// (two-pass statistics, eps 1e-5, biased variance as F.layer_norm) and keeps a running sum; the 8 warp sums are added in warp
+// order -> partial[seq][p][768].  clvp_pool_final_kernel: one CTA per sequence adds the slices in order (deterministic), applies
+// the LayerNorm affine to the mean, lat = W . mean (fp32 weights, coalesced rows), lat / max(||lat||, 1e-12) (F.normalize).
+constexpr int kPoolSlices = 8;
+
+__global__ void __launch_bounds__(256) clvp_pool_partial_kernel(const float* __restrict__ x, float* __restrict__ partial, int len) {
   __shared__ float part[8][kCD];
-  __shared__ float mean[kCD];
-  __shared__ float lat[kCD];
-  __shared__ float red[8];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int seq = blockIdx.x;
+  const int seq = blockIdx.x, slice = blockIdx.y;
   float acc[24];
 #pragma unroll
   for (int i = 0; i < 24; ++i) acc[i] = 0.f;
-  for (int r = warp; r < len; r += 8) {
+  for (int r = slice + kPoolSlices * warp; r < len; r += kPoolSlices * 8) {
     const float* xp = x + ((size_t)seq * len + r) * kCD;
     float4 v[6];
     float s = 0.f;
@@ -113,11 +112,27 @@ __global__ void __launch_bounds__(256) clvp_pool_kernel(const float* __restrict_
   for (int j = 0; j < 6; ++j)
     *reinterpret_cast<float4*>(&part[warp][128 * j + 4 * lane]) = make_float4(acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
   __syncthreads();
-  // mean of LN(x) = (sum of normalised rows / len) * weight + bias  (the affine part is the same for every row)
   for (int c = threadIdx.x; c < kCD; c += 256) {
     float s = 0.f;
 #pragma unroll
     for (int w = 0; w < 8; ++w) s += part[w][c];
+    partial[((size_t)seq * kPoolSlices + slice) * kCD + c] = s;
+  }
+}
+
+__global__ void __launch_bounds__(256) clvp_pool_final_kernel(const float* __restrict__ partial, const float* __restrict__ nw,
+                                                              const float* __restrict__ nb, const float* __restrict__ w_lat,
+                                                              float* __restrict__ lat_out, int len) {
+  __shared__ float mean[kCD];
+  __shared__ float lat[kCD];
+  __shared__ float red[8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int seq = blockIdx.x;
+  // mean of LN(x) = (sum of normalised rows / len) * weight + bias  (the affine part is the same for every row)
+  for (int c = threadIdx.x; c < kCD; c += 256) {
+    float s = 0.f;
+#pragma unroll
+    for (int p = 0; p < kPoolSlices; ++p) s += partial[((size_t)seq * kPoolSlices + p) * kCD + c];
     mean[c] = s / (float)len * nw[c] + nb[c];
   }
   __syncthreads();
@@ -216,7 +231,7 @@ struct TtsClvpHandle {
   std::vector<void*> allocs;
   ClvpEncDev enc[2];                                  // 0 = text, 1 = speech
   float* d_temp = nullptr;
-  float *d_x = nullptr, *d_rot = nullptr, *d_lat_text = nullptr, *d_lat_speech = nullptr;
+  float *d_x = nullptr, *d_rot = nullptr, *d_lat_text = nullptr, *d_lat_speech = nullptr, *d_pool = nullptr;
   __nv_bfloat16 *d_xn = nullptr, *d_qkv = nullptr, *d_ctx = nullptr, *d_h = nullptr;
   int* d_flags = nullptr;                             // [0] bad token, [1] watchdog
   int* h_flags = nullptr;                             // pinned
@@ -275,6 +290,7 @@ static int clvp_create_impl(TtsClvpHandle* h) {
   if ((rc = calloc_dev(h, &h->d_h, R * kCFF))) return rc;
   if ((rc = calloc_dev(h, &h->d_lat_text, (size_t)c.max_seqs * kCD))) return rc;
   if ((rc = calloc_dev(h, &h->d_lat_speech, (size_t)c.max_seqs * kCD))) return rc;
+  if ((rc = calloc_dev(h, &h->d_pool, (size_t)c.max_seqs * kPoolSlices * kCD))) return rc;
   if ((rc = calloc_dev(h, &h->d_temp, 4))) return rc;
   if ((rc = calloc_dev(h, &h->d_flags, 4))) return rc;
   e = cudaMemset(h->d_flags, 0, 4 * sizeof(int));
@@ -434,8 +450,9 @@ static int clvp_encode(TtsClvpHandle* h, int side, const TokT* tok, int n_seq, i
     h->launches += 7;
   }
   if (e != cudaSuccess) return ccuda(h, e, "clvp encoder kernel launch");
-  clvp_pool_kernel<<<n_seq, 256, 0, st>>>(h->d_x, E.norm_w, E.norm_b, E.w_lat, lat_out, len);
-  h->launches += 2;
+  clvp_pool_partial_kernel<<<dim3(n_seq, kPoolSlices), 256, 0, st>>>(h->d_x, h->d_pool, len);
+  clvp_pool_final_kernel<<<n_seq, 256, 0, st>>>(h->d_pool, E.norm_w, E.norm_b, E.w_lat, lat_out, len);
+  h->launches += 3;
   e = cudaGetLastError();
   if (e != cudaSuccess) return ccuda(h, e, "clvp encoder");
   return 0;

@@ -74,21 +74,23 @@ __global__ void __launch_bounds__(128) full_attn_kernel(const __nv_bfloat16* __r
     const int chunks = min(4, (len - tile * 64 + 15) >> 4);
     for (int c = 0; c < chunks; ++c) {
       const int c0 = tile * 64 + c * 16;
+      // K: B fragments of S = Q K^T (k = dim, n = position): K is [position][dim] in shared memory, i.e. already "column-major"
+      // for the mma -> plain ldmatrix; one x4 = (positions 0-7 | 8-15) x (dims kb*16 + 0-7 | 8-15)
       uint32_t kf[2][4][2];
+      {
+        const int mat = lane >> 3, r = lane & 7;
+        const uint32_t kaddr = smem_u32(kt + (c * 16 + (mat >> 1) * 8 + r) * kFaKvStride + (mat & 1) * 8);
 #pragma unroll
-      for (int j = 0; j < 2; ++j)
-#pragma unroll
-        for (int kb = 0; kb < 4; ++kb) {
-          const __nv_bfloat16* kp = kt + (c * 16 + 8 * j + g) * kFaKvStride + kb * 16 + 2 * t;
-          kf[j][kb][0] = *reinterpret_cast<const uint32_t*>(kp);
-          kf[j][kb][1] = *reinterpret_cast<const uint32_t*>(kp + 8);
-        }
+        for (int kb = 0; kb < 4; ++kb) ldmatrix_x4(kaddr + kb * 32, kf[0][kb][0], kf[0][kb][1], kf[1][kb][0], kf[1][kb][1]);
+      }
+      // V: B fragments of O += P V (k = position, n = dim): V is [position][dim] = row-major [k][n] -> ldmatrix.trans;
+      // one x4 = (positions 0-7 | 8-15) x (dims jd*8 + 0-7 | + 8-15)
       uint32_t vf[8][2];
+      {
+        const int mat = lane >> 3, r = lane & 7;
+        const uint32_t vaddr = smem_u32(vt + (c * 16 + (mat & 1) * 8 + r) * kFaKvStride + (mat >> 1) * 8);
 #pragma unroll
-      for (int jd = 0; jd < 8; ++jd) {
-        const unsigned short* vp = reinterpret_cast<const unsigned short*>(vt) + (c * 16 + 2 * t) * kFaKvStride + 8 * jd + g;
-        vf[jd][0] = (uint32_t)vp[0] | ((uint32_t)vp[kFaKvStride] << 16);
-        vf[jd][1] = (uint32_t)vp[8 * kFaKvStride] | ((uint32_t)vp[9 * kFaKvStride] << 16);
+        for (int jd = 0; jd < 8; jd += 2) ldmatrix_x4_trans(vaddr + jd * 16, vf[jd][0], vf[jd][1], vf[jd + 1][0], vf[jd + 1][1]);
       }
       float s[2][4];
 #pragma unroll

@@ -86,9 +86,12 @@ static cudaError_t launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, const
 template <int EPI>
 static cudaError_t launch_tc_auto(const CUtensorMap& a_map, const CUtensorMap& b128, const CUtensorMap& b256, const TcGemmArgs& g,
                                   int n_sm, cudaStream_t st) {
-  // wide tiles once there are enough of them to fill the machine; narrow ones for short prompts
+  // wide tiles once there are enough of them to fill the machine; narrow ones for short prompts, and when the wide tiling
+  // quantises badly over the SMs (CLVP: 63 x 3 tiles of N = 768 are 1.28 waves; 63 x 6 narrow ones 2.55 at ~0.55 of the time each)
   const int m_tiles = (g.M + kTcBM - 1) / kTcBM;
-  if (m_tiles * ((g.N + 255) / 256) >= n_sm) return launch_tc<256, EPI>(a_map, b256, g, n_sm, st);
+  const int t256 = m_tiles * ((g.N + 255) / 256), t128 = m_tiles * ((g.N + 127) / 128);
+  const int w256 = (t256 + n_sm - 1) / n_sm, w128 = (t128 + n_sm - 1) / n_sm;
+  if (t256 >= n_sm && 100 * w256 <= 55 * w128) return launch_tc<256, EPI>(a_map, b256, g, n_sm, st);
   return launch_tc<128, EPI>(a_map, b128, g, n_sm, st);
 }
 
