@@ -158,3 +158,17 @@ def test_clvp_errors_and_from_module(clvp_cls):
     again = m(text.cuda(), codes.cuda())                 # the error was reported once and cleared
     assert torch.equal(again, ok)
     m.close()
+
+
+def test_clvp_bf16_source_weights(clvp_cls):
+    """TtsClvpWeights.dtype = 1: a bfloat16 state_dict (the packing kernels' other instantiation).  The GEMM weights are
+    bf16-representable already; gains / biases / embeddings are rounded once more, so the scores move by bf16 noise only."""
+    cfg = ClvpConfig(depth=2)
+    sd = make_clvp_state_dict(cfg, seed=8)
+    text, codes = make_clvp_inputs(cfg, 4, 12, 40, seed=9)
+    m32 = clvp_cls(sd, depth=2, max_seqs=4, max_text_len=16, max_speech_len=64)
+    m16 = clvp_cls({k: v.bfloat16() for k, v in sd.items()}, depth=2, max_seqs=4, max_text_len=16, max_speech_len=64)
+    a, b = m32(text.cuda(), codes.cuda()), m16(text.cuda(), codes.cuda())
+    assert torch.isfinite(b).all() and (a - b).abs().max().item() < BF16_REL * float(sd["temperature"].exp())
+    m32.close()
+    m16.close()

@@ -114,3 +114,22 @@ def test_mel_spectrogram_matches_the_reference_goldens(golden_dir, case):
     with pytest.raises(ValueError):
         m.mel_spectrogram(torch.zeros(1, 400).cuda())
     m.close()
+
+
+def test_conditioning_bf16_source_weights():
+    """TtsArCondWeights.dtype = 1 (bfloat16 state_dict): the other instantiation of the packing kernels."""
+    import __graft_entry__ as g
+    g.build()
+    from tortoise_tts_b200 import ARGeometry, UnifiedVoiceB200
+    cfg = ARConfig(layers=1)
+    sd = dict(make_state_dict(cfg, seed=1))
+    sd.update(make_cond_state_dict(seed=47))
+    mel = make_cond_mel(1, 1, 90, seed=48)
+    m32 = UnifiedVoiceB200(sd, ARGeometry(layers=1), max_utts=1, max_seqs=2, max_text_len=16, max_new_tokens=100)
+    want = m32.get_conditioning(mel.cuda())
+    m32.close()
+    m16 = UnifiedVoiceB200({k: v.bfloat16() for k, v in sd.items()}, ARGeometry(layers=1), max_utts=1, max_seqs=2, max_text_len=16,
+                           max_new_tokens=100)
+    got = m16.get_conditioning(mel.cuda())
+    m16.close()
+    assert torch.isfinite(got).all() and rel(got, want) < BF16_REL
