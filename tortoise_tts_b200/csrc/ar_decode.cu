@@ -37,7 +37,15 @@ struct DecCfg {
   static constexpr bool kHalf = MODE == 1;
   static constexpr int kMtA = MODE == 4 ? 2 : 1;          // m-tiles a cluster multiplies in phase A
   static constexpr int kRowsA = kHalf ? 8 : 16 * kMtA;    // rows of its head a cluster owns in phase A
-  static constexpr int kLnRowsA = 16 * kMtA;              // rows it normalises for that (whole m-tiles)
+#ifdef TTS_LN1_FULL_TILE   // compile-time A/B only: MODE 1 normalises the whole m-tile as before
+  static constexpr int kLnRowsA = 16 * kMtA;
+#else
+  // rows it normalises for that: its own rows.  MODE 1: HALF an m-tile -- the c_attn epilogue keeps only the cluster's 8 rows
+  // (the sibling cluster produces the other 8), and an mma row depends on the same row of A only, so the other 8 rows of the
+  // A-operand buffer may hold anything: half the row loads and half the distributed-shared bytes of ln_1
+  // (same-box A/B 624.0 -> 614.6 us/step, profiles/r02_ab_ln1_half_tile.log)
+  static constexpr int kLnRowsA = kRowsA;
+#endif
   static constexpr int kAttnRows = kRowsA / kClusterSize; // attention rows per CTA: 2, 4, 8
   static constexpr int kWarpsPerRow = kNW / kAttnRows;    // 4, 2, 1
   static constexpr int kMtB = MODE == 1 ? 1 : 2;          // m-tiles per row group in phases B, C and the head
@@ -236,8 +244,9 @@ __device__ __forceinline__ void prefetch_next(const Params& P, const Smem& sm, i
 // piece is still incomplete (contributions land in any order).  Every wait is watchdogged.
 enum LnSrc : int { LN_SRC_X = 0, LN_SRC_XT = 1, LN_SRC_Y = 2 };
 
+// `dst0`: row of the A-operand buffer that receives row `rbase` (MODE 1 ln_1 normalises only the half m-tile its cluster owns).
 __device__ __forceinline__ void ln_cluster(const Params& P, const Smem& sm, int src, uint32_t expect, const float* gb, bool dbl, int rank,
-                                           int rbase, int npc) {
+                                           int rbase, int npc, int dst0 = 0) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   if (w >= npc) return;
   const int r = npc * rank + w;
@@ -299,7 +308,7 @@ __device__ __forceinline__ void ln_cluster(const Params& P, const Smem& sm, int 
 #pragma unroll
     for (int j = 0; j < 8; ++j) *reinterpret_cast<float4*>(lp + 128 * j + 4 * lane) = v[j];
   }
-  uint8_t* dst = sm.a_rm + (size_t)r * kARowBytes;
+  uint8_t* dst = sm.a_rm + (size_t)(dst0 + r) * kARowBytes;
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const uint2 pk = ok ? make_uint2(pack_bf16x2(v[j].x, v[j].y), pack_bf16x2(v[j].z, v[j].w)) : make_uint2(0u, 0u);
@@ -338,16 +347,32 @@ __device__ __forceinline__ void gran_load(Gran& G, const __nv_bfloat16* kvb, con
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     const int r = 4 * j + rg;
+#if defined(TTS_ATTN_DIAG) && TTS_ATTN_DIAG == 1   // timing diagnostic only (results are NOT valid): no K/V traffic
+    G.k[j] = make_uint4(0x3c003c00u + r, 0x3c003c00u, 0x3c003c00u + g, 0x3c003c00u);
+#else
     G.k[j] = (r < cnt) ? (r == pnew ? *knew : ld_cg_u4(kb + r * kHD)) : make_uint4(0u, 0u, 0u, 0u);
+#endif
   }
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     const int r = 4 * j + rg;
+#if defined(TTS_ATTN_DIAG) && TTS_ATTN_DIAG == 1
+    G.v[j] = make_uint4(0x3c003c00u + r, 0x3c003c00u, 0x3c003c00u + g, 0x3c003c00u);
+#else
     G.v[j] = (r < cnt) ? (r == pnew ? *vnew : ld_cg_u4(vb + r * kHD)) : make_uint4(0u, 0u, 0u, 0u);
+#endif
   }
 }
 
 __device__ __forceinline__ void gran_reduce(const Gran& G, const float (&qv)[8], int rg, float& m, float& l, float (&acc)[8]) {
+#if defined(TTS_ATTN_DIAG) && TTS_ATTN_DIAG == 2   // timing diagnostic only (results are NOT valid): the K/V traffic without the arithmetic
+  uint32_t x = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) x ^= G.k[j].x ^ G.k[j].y ^ G.k[j].z ^ G.k[j].w ^ G.v[j].x ^ G.v[j].y ^ G.v[j].z ^ G.v[j].w;
+  acc[0] += __uint_as_float(x & 0x3fffffffu) * qv[0];
+  m = 0.f; l = 1.f;
+  return;
+#endif
   float sc[4];
   float cm = -INFINITY;
 #pragma unroll
@@ -987,7 +1012,9 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
           build_rinfo<MODE>(P, tile_row0, attn_row0, sm, threadIdx.x, kDecThreads);
           consumer_sync();
         }
-        ln_cluster(P, sm, layer == 0 ? LN_SRC_X : LN_SRC_XT, xtag, sm.red, is_head, rank, is_head ? 0 : tile_row0, ln_warps);
+        // ln_1: the rows this cluster owns (MODE 1: rows row_lo.. of the single m-tile, placed at the same rows of the A operand)
+        const int ln_row0 = (is_head || C::kLnRowsA == 16 * C::kMtA) ? (is_head ? 0 : tile_row0) : row_lo;
+        ln_cluster(P, sm, layer == 0 ? LN_SRC_X : LN_SRC_XT, xtag, sm.red, is_head, rank, ln_row0, ln_warps, ln_row0 - (is_head ? 0 : tile_row0));
         if (!side && MODE != 4) prefetch_next(P, sm, head, pf_layer, C::kAttnRows, threadIdx.x, kDecThreads);
       }
       cluster_barrier_at<1>();
