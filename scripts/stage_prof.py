@@ -48,6 +48,14 @@ if "TTS_AR_PROF_STEP" in os.environ:
                 print("   " + " ".join(f"{int(x):4d}" for x in cl.max(axis=1)))
                 print("   per-cluster release offset ns after last arrival (max over the 4 CTAs):")
                 print("   " + " ".join(f"{int(x):4d}" for x in (rel - arr.max()).reshape(32, 4).max(axis=1)))
+    aw = raw[10240:10240 + 128 * 16].reshape(128, 16)
+    if aw.any():
+        dur = (aw[:, :8] - aw[:, 8:16]) / 1e3          # per (CTA, warp): q arrived -> granule loop done, us
+        start = aw[:, 8:16].min()
+        end = (aw[:, :8] - start) / 1e3
+        print("attention of layer 3, per warp (row = w >> 2, quarter = w & 3 at 16 rows): granule-loop us, mean / max over the 128 CTAs")
+        print("   " + "  ".join(f"w{w}: {dur[:, w].mean():.2f}/{dur[:, w].max():.2f}" for w in range(8)))
+        print(f"   CTA-level (slowest warp): mean {dur.max(axis=1).mean():.2f} us, max {dur.max():.2f}; last warp of the grid ends {end.max():.2f} us after the first q")
     raw = raw[:1024 + 4096]
     t = raw[: 2 * n_instr].reshape(n_instr, 2)
     marks = raw[1024:].reshape(-1, 2)

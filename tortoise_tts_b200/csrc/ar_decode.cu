@@ -332,6 +332,9 @@ struct Gran {
 __device__ __forceinline__ void gran_load(Gran& G, const __nv_bfloat16* kvb, const int* pt, int g, int Gp, int plen, int len,
                                           int rg, int pnew = -1, const uint4* knew = nullptr, const uint4* vnew = nullptr) {
   int pos0, cnt, page;
+#if defined(TTS_ATTN_DIAG) && TTS_ATTN_DIAG == 3   // timing diagnostic only (results are NOT valid): all K/V reads hit the shared prompt pages
+  if (g >= Gp) g = (g - Gp) % (Gp > 1 ? Gp - 1 : 1);
+#endif
   if (g < Gp) {
     pos0 = 16 * g;
     cnt = min(16, plen - pos0);
@@ -473,6 +476,7 @@ __device__ void attn_local(const Params& P, int layer, int head, int attn_row0, 
         auto load = [&](Gran& Gx, int g) { gran_load(Gx, kvb, pt, g, Gp, plen, len, rg, g == g_new ? p_new : -1, knew, vnew); };
         // (requesting the first granules of old positions before this wait was measured neutral: 622.6 vs 622.0 us/step)
         if (QkvAsync<MODE>::on && !mbar_wait(&sm.ctrl->qbar, q_phase, &sm.ctrl->abort_flag)) *reinterpret_cast<volatile int*>(P.watchdog) = 1;
+        if (P.prof && layer == 3 && sm.ctrl->ibuf[2] && lane == 0) P.prof[10240 + blockIdx.x * 16 + 8 + w] = globaltimer_ns();
 #pragma unroll
         for (int i = 0; i < NG - 1; ++i)
           if (g0 + i < g1) load(G[i], g0 + i);
@@ -503,6 +507,7 @@ __device__ void attn_local(const Params& P, int layer, int head, int attn_row0, 
       }
     }
     prof_mark(P, sm.ctrl, 12);
+    if (P.prof && layer == 3 && sm.ctrl->ibuf[2] && lane == 0) P.prof[10240 + blockIdx.x * 16 + w] = globaltimer_ns();
     while (q < (s + 1) * QPW) flush();                 // the last quarter, and quarters without a granule (empty partials)
   }
   consumer_sync();
@@ -967,6 +972,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) ar_decode_kernel(const __grid_
   ins.row0 = 0; ins.nrows = n; ins.flags = 0; ins.rot = 0; ins.pad0 = ins.pad1 = 0;
   for (int step = 0; step < P.n_steps && alive; ++step) {
     if (blockIdx.x == 0 && threadIdx.x == 0) c->ibuf[1] = (P.prof && step == P.prof_step) ? 1 : 0;
+    if (threadIdx.x == 0) c->ibuf[2] = (P.prof && step == P.prof_step) ? 1 : 0;   // every CTA: per-warp attention times of layer 3
     prof_mark(P, c, 100 + OP_SAMPLE);
     alive = dec_grid_barrier(P, sm, epoch, fd, 0);
     if (!alive) break;
