@@ -1,10 +1,6 @@
 #!/bin/bash
-# what bounds the decode attention: timing-only variants (results invalid) and per-warp granule-loop times of every CTA
+# decode attention: PV accumulation as paired fp32 FMAs (FFMA2, bit-identical) | + QK in two chains; same-box A/B, parity
 mkdir -p gpurun_out
-cp tortoise_tts_b200/lib/libtts_ar.so /tmp/base.so
-for v in base attn_nomath attn_l2only; do
-  if [ $v = base ]; then cp /tmp/base.so tortoise_tts_b200/lib/libtts_ar.so; else cp ab/libtts_ar_$v.so tortoise_tts_b200/lib/libtts_ar.so; fi
-  TTS_AR_PROF_STEP=200 timeout 300 python scripts/stage_prof.py 16 300 > gpurun_out/stage_prof_16_$v.log 2>&1
-  echo "== $v"; grep -E "^N=|w0:|CTA-level|attention of" gpurun_out/stage_prof_16_$v.log; grep -A32 "marks of layer 3" gpurun_out/stage_prof_16_$v.log | grep -E "attn"
-done
-cp /tmp/base.so tortoise_tts_b200/lib/libtts_ar.so
+bash scripts/ab_run.sh "16 300" base pre qkffma2 > gpurun_out/ab_attention_ffma2.log 2>&1; cat gpurun_out/ab_attention_ffma2.log
+bash scripts/ab_run.sh "64 300" base pre qkffma2 > gpurun_out/ab_attention_ffma2_64.log 2>&1; cat gpurun_out/ab_attention_ffma2_64.log
+timeout 1500 python -m pytest tests/test_gpu_parity.py -m gpu -x -q > gpurun_out/pytest_parity.log 2>&1; tail -3 gpurun_out/pytest_parity.log

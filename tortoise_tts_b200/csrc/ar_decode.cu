@@ -380,6 +380,7 @@ __device__ __forceinline__ void gran_reduce(const Gran& G, const float (&qv)[8],
   float cm = -INFINITY;
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
+#ifndef TTS_ATTN_QK_FFMA2
     float s = qv[0] * bf16_lo(G.k[j].x);
     s = fmaf(qv[1], bf16_hi(G.k[j].x), s);
     s = fmaf(qv[2], bf16_lo(G.k[j].y), s);
@@ -388,6 +389,13 @@ __device__ __forceinline__ void gran_reduce(const Gran& G, const float (&qv)[8],
     s = fmaf(qv[5], bf16_hi(G.k[j].z), s);
     s = fmaf(qv[6], bf16_lo(G.k[j].w), s);
     s = fmaf(qv[7], bf16_hi(G.k[j].w), s);
+#else   // A/B: even / odd dims in two chains (different summation order: NOT bit-identical to the scalar chain)
+    float s = qv[0] * bf16_lo(G.k[j].x), s1 = qv[1] * bf16_hi(G.k[j].x);
+    ffma2(s, s1, qv[2], qv[3], bf16_lo(G.k[j].y), bf16_hi(G.k[j].y));
+    ffma2(s, s1, qv[4], qv[5], bf16_lo(G.k[j].z), bf16_hi(G.k[j].z));
+    ffma2(s, s1, qv[6], qv[7], bf16_lo(G.k[j].w), bf16_hi(G.k[j].w));
+    s += s1;
+#endif
     s += __shfl_xor_sync(0xffffffffu, s, 1);
     s += __shfl_xor_sync(0xffffffffu, s, 2);
     s += __shfl_xor_sync(0xffffffffu, s, 4);
@@ -405,6 +413,7 @@ __device__ __forceinline__ void gran_reduce(const Gran& G, const float (&qv)[8],
   for (int j = 0; j < 4; ++j) {
     const float pj = exp2f(sc[j] - m_new);          // masked rows: exp2(-inf) = 0
     l += pj;
+#ifdef TTS_ATTN_NO_FFMA2
     acc[0] = fmaf(pj, bf16_lo(G.v[j].x), acc[0]);
     acc[1] = fmaf(pj, bf16_hi(G.v[j].x), acc[1]);
     acc[2] = fmaf(pj, bf16_lo(G.v[j].y), acc[2]);
@@ -413,6 +422,12 @@ __device__ __forceinline__ void gran_reduce(const Gran& G, const float (&qv)[8],
     acc[5] = fmaf(pj, bf16_hi(G.v[j].z), acc[5]);
     acc[6] = fmaf(pj, bf16_lo(G.v[j].w), acc[6]);
     acc[7] = fmaf(pj, bf16_hi(G.v[j].w), acc[7]);
+#else   // the same eight fma.rn as four paired instructions (bit-identical)
+    ffma2(acc[0], acc[1], pj, pj, bf16_lo(G.v[j].x), bf16_hi(G.v[j].x));
+    ffma2(acc[2], acc[3], pj, pj, bf16_lo(G.v[j].y), bf16_hi(G.v[j].y));
+    ffma2(acc[4], acc[5], pj, pj, bf16_lo(G.v[j].z), bf16_hi(G.v[j].z));
+    ffma2(acc[6], acc[7], pj, pj, bf16_lo(G.v[j].w), bf16_hi(G.v[j].w));
+#endif
   }
   m = m_new;
 }
@@ -463,7 +478,11 @@ __device__ void attn_local(const Params& P, int layer, int head, int attn_row0, 
       const int g0 = (s * QPW * Gt) >> 2, g1 = ((s + 1) * QPW * Gt) >> 2;
       if (g1 > g0) {
         const int* pt = ri + 80 + 64 * j;
+#if defined(TTS_ATTN_DIAG) && TTS_ATTN_DIAG == 4   // timing diagnostic only (results are NOT valid): every layer reads layer 0's K/V (L2-resident)
+        const __nv_bfloat16* kvb = P.kv + kv_row_offset(0, P.n_pages, 0, 0, head, 0) + dc * 8;
+#else
         const __nv_bfloat16* kvb = P.kv + kv_row_offset(layer, P.n_pages, 0, 0, head, 0) + dc * 8;
+#endif
 #ifndef TTS_ATTN_DEPTH
 #define TTS_ATTN_DEPTH 3
 #endif
