@@ -707,6 +707,18 @@ __device__ void proj_splitk(const Params& P, int rank, int row_lo, int tile_row0
 #pragma unroll
     for (int j = 0; j < 4; ++j) a[mt][j] = ctx_smem(sm)[(mt * 4 + j) * 32 + lane];
   const int g = lane >> 2, t = lane & 3;
+  // MODE 1 / 2: the contributions of the cluster's rows go to y as ONE bulk reduction per row (cp.reduce.async.bulk .add.u64:
+  // 2 KiB = this CTA's 256 columns of a row) from a staging tile in the A-operand buffer, instead of 2048 (4096) 64-bit red.global
+  // per CTA -- an SM issues those at ~1.3 clocks per lane, which was ~1 us of every block's attention -> ln_2 hand-off.  Same
+  // integer adds at L2, same words (value + count): bit-identical.  The staging row of global row R is row R of the A-operand
+  // buffer: ln_1's rows went into registers at c_attn, and ln_2 (this CTA's or a peer's distributed-shared store) writes row R
+  // only after y's row R is complete, i.e. after this reduction has read its source.
+#ifdef TTS_PROJ_RED
+  constexpr bool kBulk = false;
+#else
+  constexpr bool kBulk = C::kMtA == 1;
+#endif
+  constexpr int kStageRow = kARowBytes;
   wait_chunks(c, pipe, 2);
 #pragma unroll
   for (int ch = 0; ch < 2; ++ch) {
@@ -740,6 +752,14 @@ __device__ void proj_splitk(const Params& P, int rank, int row_lo, int tile_row0
       for (int hh = 0; hh < 2; ++hh) {
         if (C::kHalf && hh != (row_lo >> 3)) continue;             // the other half of the tile is the sibling cluster's
         const int row = tile_row0 + 16 * mt + 8 * hh + g;
+        if (kBulk) {
+          const int lr = row_lo + (C::kHalf ? 0 : 8 * hh) + g;         // == the global row (phase-B row groups start at 0 in these modes)
+#pragma unroll
+          for (int tt = 0; tt < 2; ++tt)
+            *reinterpret_cast<longlong2*>(sm.a_rm + (size_t)lr * kStageRow + (size_t)(128 * ch + 16 * w + 2 * t + 8 * tt) * 8) =
+                make_longlong2(cnt_contrib(acc[mt][tt][2 * hh]), cnt_contrib(acc[mt][tt][2 * hh + 1]));
+          continue;
+        }
         if (row >= P.n_rows) continue;
 #pragma unroll
         for (int tt = 0; tt < 2; ++tt) {
@@ -748,6 +768,14 @@ __device__ void proj_splitk(const Params& P, int rank, int row_lo, int tile_row0
           red_add_s64(yp + 1, cnt_contrib(acc[mt][tt][2 * hh + 1]));
         }
       }
+  }
+  if (kBulk) {
+    fence_proxy_async();                 // the staged words (generic-proxy stores) are read by the bulk engine
+    consumer_sync();
+    if (w == 0 && lane < C::kRowsA) {
+      const int row = row_lo + lane;
+      if (row < P.n_rows) bulk_red_add_u64(P.y + (size_t)row * kD + 256 * rank, sm.a_rm + (size_t)row * kStageRow, 2048u);
+    }
   }
 }
 

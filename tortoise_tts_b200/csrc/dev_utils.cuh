@@ -72,6 +72,14 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
       : "memory");
 }
 
+// Bulk reduction shared -> global (UBLKRED): y[i] += buf[i] for `bytes` / 8 unsigned 64-bit words, each element an atomic add at L2,
+// issued by one thread as one instruction; the group is committed at once (the source must stay untouched until the adds are done)
+__device__ __forceinline__ void bulk_red_add_u64(void* gdst, const void* src_smem, uint32_t bytes) {
+  asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.u64 [%0], [%1], %2;\n\tcp.async.bulk.commit_group;" ::"l"(gdst),
+               "r"(smem_u32(src_smem)), "r"(bytes)
+               : "memory");
+}
+
 // 16-byte asynchronous copy global (L2, never L1) -> shared, and the wait for all of this thread's copies
 __device__ __forceinline__ void cp_async_cg16(void* smem_dst, const void* gsrc) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
