@@ -1,7 +1,4 @@
 #!/bin/bash
-# LayerNorm gain staging overlapped with the row polls (no second CTA barrier at a soft boundary) + refills issued by warp 7: parity, same-box A/B
+# refill bursts per boundary (before ln_2 / grid barrier / before ln_1): 6/6/6 (base) vs 4/6/6, 2/8/6, 6/8/2, 4/8/4
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests/test_gpu_parity.py -m gpu -x -q > gpurun_out/pytest_parity.log 2>&1; tail -3 gpurun_out/pytest_parity.log
-bash scripts/ab_run.sh "16 300" base pre feed0 feed7nolap > gpurun_out/ab_stage_overlap.log 2>&1; cat gpurun_out/ab_stage_overlap.log
-bash scripts/ab_run.sh "32 300" base pre > gpurun_out/ab_stage_overlap_32.log 2>&1; cat gpurun_out/ab_stage_overlap_32.log
-bash scripts/ab_run.sh "64 300" base pre > gpurun_out/ab_stage_overlap_64.log 2>&1; cat gpurun_out/ab_stage_overlap_64.log
+bash scripts/ab_run.sh "16 300" base v466 v286 v682 v484 > gpurun_out/ab_refill_schedule.log 2>&1; cat gpurun_out/ab_refill_schedule.log
