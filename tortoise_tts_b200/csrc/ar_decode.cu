@@ -484,9 +484,13 @@ __device__ void attn_local(const Params& P, int layer, int head, int attn_row0, 
         const __nv_bfloat16* kvb = P.kv + kv_row_offset(layer, P.n_pages, 0, 0, head, 0) + dc * 8;
 #endif
 #ifndef TTS_ATTN_DEPTH
-#define TTS_ATTN_DEPTH 3
+#define TTS_ATTN_DEPTH 2
 #endif
-        constexpr int NG = TTS_ATTN_DEPTH;             // granules in flight per warp (4 KiB each), a register ring
+        // granules per warp in the register ring (4 KiB each).  2 = the next granule's loads are in flight while one is reduced.
+        // Same-box A/B on the final build of round 2 (profiles/r02_ab_attention_depth_final.log): depth 2 / 3 / 4 = 597.4 / 600.4 /
+        // 606.2 us/step at 16 rows, 835.7 / 844.4 at 32, 1379 / 1418 at 64, depth 1 670.5 vs 658.6 (520 steps): the phase is not
+        // short of bytes in flight, and 32 registers fewer per ring slot help everything around it.
+        constexpr int NG = TTS_ATTN_DEPTH;
         Gran G[NG];
         // the granule that holds the position this layer's c_attn has just produced (always the last private one)
         const int g_new = QkvAsync<MODE>::on ? Gt - 1 : -2, p_new = (len - 1 - plen) & 15;
