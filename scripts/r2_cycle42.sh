@@ -1,5 +1,4 @@
 #!/bin/bash
-# attention ring depth 2 as the default: parity of the decode kernels
+# back-off between polls of the residual stream / the counting accumulator (ln_1 / ln_2): 0 (base) vs 50 ns vs 200 ns
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests/test_gpu_parity.py -m gpu -x -q > gpurun_out/pytest_parity.log 2>&1; tail -3 gpurun_out/pytest_parity.log
-bash scripts/ab_run.sh "16 300" base pre > gpurun_out/ab_depth2_confirm.log 2>&1; cat gpurun_out/ab_depth2_confirm.log
+bash scripts/ab_run.sh "16 300" base sleep50 sleep200 > gpurun_out/ab_poll_backoff.log 2>&1; cat gpurun_out/ab_poll_backoff.log
